@@ -1,0 +1,245 @@
+#!/usr/bin/env python
+"""bench.py -- headline benchmark of the local provider's hot path (BASELINE.json configs[1]).
+
+A "step" is one provider query: prefill a 512-token prompt, then greedy-decode 256 tokens, on a
+Llama-3.2-1B-shaped random-init bf16 model, one model instance per GPU (the runner's fan-out maps
+model i to GPU i with no collective, /root/reference/internal/runner/runner.go:62-95), seeds =
+ranks.  Whole-job metric: generated tokens per second over all GPUs.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
+
+For N > 1 launch under torchrun (one rank per GPU); torch.distributed is used only for the
+barrier and the max-over-ranks reduction -- the measured path is libllmc.so through its C ABI.
+
+--impl reference times the CPU implementation of the same path (the fp32 oracle, all host
+threads) on a bounded sample of the workload; see `cpu_baseline.sample`.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+PROMPT_LEN, NEW_TOKENS, DECODE_CHUNK = 512, 256, 64
+SHAPE_1B = dict(hidden=2048, layers=16, q_heads=32, kv_heads=8, head_dim=64, inter=8192, vocab=128256, tied=1)
+METRIC = "decode tok/s (generated tokens / s over all GPUs; the 512-token prefill is inside the timed region)"
+
+
+def peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        d = json.load(open(p))
+        return float(d["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+class ClockSampler(threading.Thread):
+    """nvidia-smi clocks / throttle reasons sampled during the timed region."""
+    Q = "clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown," \
+        "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+
+    def __init__(self, index):
+        super().__init__(daemon=True)
+        self.index, self.rows, self.stop_flag = index, [], False
+
+    def run(self):
+        while not self.stop_flag:
+            try:
+                out = subprocess.run(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
+                                      "--format=csv,noheader,nounits"], capture_output=True, text=True, timeout=5).stdout
+                parts = [x.strip() for x in out.strip().split(",")]
+                if len(parts) >= 6:
+                    self.rows.append(parts)
+            except Exception:
+                pass
+            time.sleep(0.2)
+
+    def summary(self):
+        self.stop_flag = True
+        self.join(timeout=6)
+        if not self.rows:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        sm = sorted(float(r[0]) for r in self.rows)
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = [n for i, n in enumerate(names) if any(r[2 + i].lower().startswith("active") for r in self.rows)]
+        return {"sm_mhz": sm[len(sm) // 2], "sm_max_mhz": float(self.rows[0][1]), "reasons": reasons,
+                "samples": len(self.rows)}
+
+
+def cpu_sample(threads_all=True, prompt_len=64, new_tokens=32, steps=1, warmup=0):
+    """The fp32 CPU oracle on a bounded sample of the workload (same shape, same prompt/decode ratio)."""
+    from oracle import ref
+    o = ref.Oracle("llama-1b", seed=0, max_ctx=prompt_len + new_tokens + 8)
+    prompt = np.random.default_rng(1).integers(0, 128256, prompt_len)
+    times = []
+    for i in range(warmup + steps):
+        o.reset()
+        t0 = time.perf_counter()
+        o.generate(prompt, new_tokens)
+        if i >= warmup:
+            times.append(time.perf_counter() - t0)
+    dt = sum(times)
+    return {"value": new_tokens * len(times) / dt, "unit": "tok/s", "cores": ref.num_threads(), "kind": "port",
+            "sample": "fp32 C++/OpenMP oracle (oracle/llama_ref.cpp), Llama-3.2-1B shape, %d-token prompt + %d greedy "
+                      "tokens per step (the 512+256 workload scaled 1/8, same 2:1 ratio), %d step(s), %.1f s"
+                      % (prompt_len, new_tokens, len(times), dt)}, dt / len(times)
+
+
+def run_reference(args, rank, world):
+    if rank != 0:
+        return
+    base, ms = cpu_sample(steps=args.steps, warmup=min(args.warmup, 1))
+    line = {"impl": "reference", "metric": METRIC, "value": base["value"], "unit": "tok/s", "n_gpus": args.gpus,
+            "steps": args.steps, "warmup": min(args.warmup, 1), "ms_per_step": ms * 1e3, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": "local provider query, Llama-3.2-1B shape random-init, 512-token prompt + 256 greedy "
+                                   "tokens (BASELINE.json configs[1]); CPU arm runs a 1/8 sample per step",
+                       "shape": "llama-3.2-1b", "prompt": PROMPT_LEN, "new_tokens": NEW_TOKENS, "batch": 1},
+            "cpu_baseline": base,
+            "e2e": {"value": base["value"], "unit": "tok/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0,
+            "note": "the reference repository has no local inference (remote HTTP providers only) and Go is not "
+                    "installed; the CPU arm is the oracle port of the north-star fp32 forward on all host threads"}
+    print(json.dumps(line), flush=True)
+
+
+def run_ours(args, rank, world, local_rank):
+    import llm_consensus_b200.llmc as llmc
+    dist = None
+    if world > 1:
+        import torch
+        import torch.distributed as dist
+        torch.cuda.set_device(local_rank)
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+
+    def barrier():
+        if dist is not None:
+            dist.barrier()
+
+    def allmax(v):
+        if dist is None:
+            return v
+        import torch
+        t = torch.tensor([v], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    def allsum(v):
+        if dist is None:
+            return v
+        import torch
+        t = torch.tensor([v], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.SUM)
+        return float(t.item())
+
+    if llmc.device_count() < 1:
+        raise SystemExit("bench.py: no CUDA device -- libllmc has no CPU fallback")
+    eng = llmc.Engine(shape=llmc.SHAPE_LLAMA_1B, device=local_rank, seed=rank, max_ctx=1024, max_slots=2)
+    prompt = np.random.default_rng(1).integers(0, 128256, PROMPT_LEN).astype(np.int32)
+
+    def step():
+        """One provider query through the C ABI with host buffers.  Returns (device ms prefill, device ms decode)."""
+        slot = eng.seq_alloc()
+        eng.prefill(slot, prompt)
+        pre = eng.stats()["last_prefill_ms"]
+        dec, left = 0.0, NEW_TOKENS - 1
+        while left > 0:
+            k = min(DECODE_CHUNK, left)
+            eng.decode([slot], k)
+            dec += eng.stats()["last_decode_ms"]
+            left -= k
+        eng.seq_free(slot)
+        return pre, dec
+
+    for _ in range(max(args.warmup, 3)):
+        step()
+    sampler = ClockSampler(local_rank)
+    sampler.start()
+    launches0 = eng.stats()["kernel_launches"]
+    barrier()
+    t0 = time.perf_counter()
+    dev_pre = dev_dec = 0.0
+    for _ in range(args.steps):
+        p, d = step()
+        dev_pre += p
+        dev_dec += d
+    barrier()
+    wall = time.perf_counter() - t0
+    clocks = sampler.summary()
+    launches = eng.stats()["kernel_launches"] - launches0
+    st = eng.stats()
+
+    dev_ms = allmax(dev_pre + dev_dec)          # device time (CUDA events on the engine's stream), max over ranks
+    wall_s = allmax(wall)
+    dec_ms = allmax(dev_dec)
+    pre_ms = allmax(dev_pre)
+    launches_all = allsum(float(launches))
+    tokens_all = NEW_TOKENS * args.steps * world
+    value = tokens_all / (dev_ms / 1e3)
+    e2e = tokens_all / wall_s
+    # roofline of the decode step (one CUDA-graph launch = 81 kernels): algorithmic bytes / device time
+    steps_dec = (NEW_TOKENS - 1) * args.steps
+    avg_ctx = PROMPT_LEN + (NEW_TOKENS - 1) / 2.0
+    bytes_per_step = st["weight_bytes"] + (avg_ctx + 1) * st["kv_bytes_per_token"]
+    step_s = dec_ms / 1e3 / steps_dec
+    peak, peak_src = peaks()
+    achieved = bytes_per_step / step_s / 1e9
+    line = {
+        "metric": METRIC, "value": value, "unit": "tok/s", "n_gpus": world, "steps": args.steps,
+        "warmup": max(args.warmup, 3), "ms_per_step": dev_ms / args.steps, "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
+        "config": {"workload": "local provider query, Llama-3.2-1B shape random-init bf16, 512-token prompt + 256 greedy "
+                               "tokens, batch 1 per GPU (BASELINE.json configs[1]); one model instance (seed = rank) per GPU, "
+                               "no collective",
+                   "shape": "llama-3.2-1b", "prompt": PROMPT_LEN, "new_tokens": NEW_TOKENS, "batch": 1,
+                   "l2": "no flush needed: each decode step streams 2.47 GB of weights, 20x the 126 MB L2",
+                   "graph": st["graph_enabled"], "pdl": st["pdl_enabled"]},
+        "decode_only_tok_s_per_gpu": steps_dec / (dec_ms / 1e3),
+        "prefill_ms": pre_ms / args.steps,
+        "queries_per_s": args.steps * world / (dev_ms / 1e3),
+        "e2e": {"value": e2e, "unit": "tok/s", "h2d_bytes_per_step": PROMPT_LEN * 4 + 8,
+                "d2h_bytes_per_step": NEW_TOKENS * 4,
+                "what": "wall clock around the llmc_prefill/llmc_decode C-ABI calls with host token buffers "
+                        "(H2D of the prompt ids and D2H of the generated ids every step)"},
+        "gpu_launches": int(launches_all),
+        "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                     "traffic": None, "peak_source": peak_src, "frac_of_8TBs_nominal": achieved / 8000.0,
+                     "kernel": "one decode step = one CUDA-graph launch of 5 kernels/layer x 16 + LM head",
+                     "algorithmic_bytes_per_launch": bytes_per_step, "avg_launch_us": step_s * 1e6},
+        "clocks": clocks,
+    }
+    if rank == 0 and world == 1 and not args.no_cpu:
+        line["cpu_baseline"], _ = cpu_sample()
+    if rank == 0:
+        print(json.dumps(line), flush=True)
+    eng.close()
+    if dist is not None:
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    args = ap.parse_args()
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.impl == "reference":
+        run_reference(args, rank, world)
+    else:
+        run_ours(args, rank, world, local_rank)
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,73 @@
+/* llmc_ops.h -- kernel-level test and bench hooks exported by libllmc.so.
+ *
+ * These are NOT part of the provider boundary (that is include/llmc.h).  They let the parity
+ * tests drive single kernels of the hot path with host buffers and compare them with the CPU
+ * oracle; each call allocates its device buffers, runs, copies back and frees.  They have no
+ * counterpart in the reference, whose providers hold no arithmetic
+ * (/root/reference/internal/provider/provider.go:13-21).
+ *
+ * All return 0 or a negative LLMC_ERR_* code; llmc_ops_last_error() has the message.
+ * bf16 data crosses the boundary as uint16_t bit patterns.
+ */
+#ifndef LLMC_OPS_H
+#define LLMC_OPS_H
+
+#include <stdint.h>
+#include "llmc.h"
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+const char* llmc_ops_last_error(void);
+
+/* Decode GEMV: y[b][n] (+)= sum_k W[n][k] * xhat[b][k], B <= 8, K % 256 == 0, N % 2 == 0.
+ * norm != 0: xhat = RMSNorm(x; gain, eps) fused in the prologue; resid != 0: y += (y is in/out). */
+int llmc_op_gemv(int device, int N, int K, int B, const uint16_t* W, const float* x, int norm,
+                 const uint16_t* gain, float eps, int resid, float* y);
+
+/* Fused gate/up GEMV + SwiGLU on logical matrices Wg, Wu [I][K] (packed/interleaved inside):
+ * act[b][j] = silu(Wg xhat)_j * (Wu xhat)_j with xhat = RMSNorm(x; gain, eps). */
+int llmc_op_gemv_swiglu(int device, int I, int K, int B, const uint16_t* Wg, const uint16_t* Wu, const float* x,
+                        const uint16_t* gain, float eps, float* act);
+
+/* LM head + greedy argmax: logits[b][n] (may be NULL) and tok[b] = lowest-index argmax. */
+int llmc_op_lmhead(int device, int V, int K, int B, const uint16_t* W, const float* x, const uint16_t* gain,
+                   float eps, float* logits, int32_t* tok);
+
+/* Single-query attention over a paged cache built from dense K/V:
+ *   q [B][q_heads*d] fp32; k, v [B][max_ctx][kv_heads*d] bf16; ctx[b] tokens valid; out like q.
+ * nsplit = 0 picks the engine's default.  Pages are assigned in a scrambled order. */
+int llmc_op_attn_decode(int device, int B, int q_heads, int kv_heads, int head_dim, int page_size, int nsplit,
+                        int max_ctx, const int32_t* ctx, const float* q, const uint16_t* k, const uint16_t* v,
+                        float* out);
+
+/* Prefill GEMM C = A W^T.  impl 0: tcgen05; 1: plain CUDA-core comparator.  epi: 0 bf16 store,
+ * 1 f32 store, 2 f32 residual add (out is in/out), 3 SwiGLU on logical Wg|Wu given as
+ * W = [Wg ; Wu] ([2I][K], packed inside), out bf16 [T][I]. */
+int llmc_op_gemm(int device, int impl, int epi, int T, int N, int K, const uint16_t* A, const uint16_t* W,
+                 void* out);
+
+/* Row-wise RMSNorm fp32 -> bf16. */
+int llmc_op_rmsnorm_rows(int device, int T, int H, const float* x, const uint16_t* gain, float eps, uint16_t* out);
+
+/* RoPE + KV append + causal attention of T new rows at positions p0..p0+T-1:
+ *   qkv [T][(nq+2nkv)*d] fp32 (pre-RoPE) for the new rows; k_past, v_past [p0][nkv*d] bf16
+ *   (already rotated) for the cached prefix; out bf16 [T][nq*d]; q_out bf16 [T][nq*d];
+ *   k_new, v_new bf16 [T][nkv*d] read back from the pages. */
+int llmc_op_prefill_attention(int device, int T, int p0, int q_heads, int kv_heads, int head_dim, int page_size,
+                              float rope_theta, const float* qkv, const uint16_t* k_past, const uint16_t* v_past,
+                              uint16_t* out, uint16_t* q_out, uint16_t* k_new, uint16_t* v_new);
+
+/* Read a LOGICAL weight tensor of an engine back (un-packing the HBM layout); kinds as in the
+ * oracle: layer -1: 0 embedding, 1 lm head, 2 final gain; layer >= 0: 0 g1, 1 wq, 2 wk, 3 wv,
+ * 4 wo, 5 g2, 6 wg, 7 wu, 8 wd.  Returns the element count (or < 0); copies if cap suffices. */
+int64_t llmc_debug_tensor(llmc_engine* e, int layer, int kind, uint16_t* out, int64_t cap);
+
+/* Read the cached K and V rows ([kv_heads*d] bf16 each) of one position of a slot. */
+int llmc_debug_kv(llmc_engine* e, int slot, int layer, int pos, uint16_t* k, uint16_t* v);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* LLMC_OPS_H */

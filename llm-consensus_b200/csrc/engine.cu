@@ -1,0 +1,629 @@
+// engine.cu -- the inference engine behind the C ABI in include/llmc.h: one model instance on
+// one GPU (weights generated in HBM from a seed, paged bf16 KV pool, prefill and decode
+// schedules over the kernels in this directory).
+//
+// It stands where a remote backend's HTTP round trip is in the reference:
+// QueryStream in /root/reference/internal/provider/openai.go:141-210 sends the prompt and then
+// scans SSE lines; a local provider calls llmc_prefill() and then loops over llmc_decode().
+//
+// HBM layout (per engine):
+//   weights   one blob, bf16, every matrix row-major [out][in] (K-major: the same bytes feed
+//             the decode GEMV stream and the TMA tiles of the prefill GEMM)
+//               per layer: g1[H] | Wqkv[(nq+2nkv)d][H] | Wo[H][nq d] | g2[H] |
+//                          Wgu[2I][H] (gate/up interleaved in blocks of 64 rows) | Wd[H][I]
+//               global:    E[V][H] | LMHead[V][H] (= E when tied) | gf[H]
+//   KV pool   K and V: [layer][page][kv_head][page_size][d] bf16; block table [slot][page]
+//   decode    x[B][H], q[B][nq d], attn[B][nq d], act[B][I] fp32; split-attention scratch
+//   prefill   x[T][H] fp32, xn[T][H] bf16, qkv[T][(nq+2nkv)d] fp32, q/attn[T][nq d] bf16,
+//             act[T][I] bf16 for T = prefill_chunk
+#include <cuda_runtime.h>
+#include <math.h>
+#include <string.h>
+#include <algorithm>
+#include <map>
+#include <mutex>
+#include <string>
+#include <vector>
+#include "../../include/llmc.h"
+#include "engine_internal.h"
+
+using namespace llmc;
+
+namespace {
+thread_local std::string g_create_error;
+}  // namespace
+
+namespace {
+
+int fail(llmc_engine* e, int code, const std::string& msg) {
+  if (e) e->last_error = msg;
+  else g_create_error = msg;
+  return code;
+}
+
+#define E_TRY(expr)                                                                                        \
+  do {                                                                                                     \
+    cudaError_t _e = (expr);                                                                               \
+    if (_e != cudaSuccess)                                                                                 \
+      return fail(e, _e == cudaErrorMemoryAllocation ? LLMC_ERR_OOM : LLMC_ERR_CUDA,                       \
+                  std::string(#expr) + ": " + cudaGetErrorString(_e) + " (engine.cu:" + std::to_string(__LINE__) + ")"); \
+  } while (0)
+
+template <typename T>
+int dalloc(llmc_engine* e, T** p, size_t n) {
+  void* v = nullptr;
+  E_TRY(cudaMalloc(&v, n * sizeof(T) + 256));
+  e->allocs.push_back(v);
+  *p = reinterpret_cast<T*>(v);
+  return LLMC_OK;
+}
+
+int apply_shape(llmc_config& c) {
+  if (c.shape == LLMC_SHAPE_LLAMA_1B) {
+    c.hidden = 2048; c.layers = 16; c.q_heads = 32; c.kv_heads = 8; c.head_dim = 64; c.inter = 8192;
+    c.vocab = 128256; c.tied = 1;
+  } else if (c.shape == LLMC_SHAPE_LLAMA_8B) {
+    c.hidden = 4096; c.layers = 32; c.q_heads = 32; c.kv_heads = 8; c.head_dim = 128; c.inter = 14336;
+    c.vocab = 128256; c.tied = 0;
+  } else if (c.shape != LLMC_SHAPE_CUSTOM) {
+    return LLMC_ERR_INVALID;
+  }
+  return LLMC_OK;
+}
+
+std::string validate(const llmc_config& c) {
+  auto bad = [](const char* s) { return std::string("unsupported shape: ") + s; };
+  if (c.hidden < 256 || c.hidden % 256) return bad("hidden must be a positive multiple of 256");
+  if (c.layers < 1) return bad("layers < 1");
+  if (c.head_dim != 32 && c.head_dim != 64 && c.head_dim != 128) return bad("head_dim must be 32, 64 or 128");
+  if (c.kv_heads < 1 || c.q_heads % c.kv_heads) return bad("q_heads must be a multiple of kv_heads");
+  int g = c.q_heads / c.kv_heads;
+  if (g != 1 && g != 2 && g != 4 && g != 8) return bad("q_heads/kv_heads must be 1, 2, 4 or 8");
+  if ((c.q_heads * c.head_dim) % 256) return bad("q_heads*head_dim must be a multiple of 256");
+  if (((c.q_heads + 2 * c.kv_heads) * c.head_dim) % 64) return bad("(q_heads+2*kv_heads)*head_dim must be a multiple of 64");
+  if (c.inter < 256 || c.inter % 256) return bad("inter must be a positive multiple of 256");
+  if (c.vocab < 4 || c.vocab % 4) return bad("vocab must be a positive multiple of 4");
+  if (c.page_size < 32 || c.page_size % 32) return "page_size must be a positive multiple of 32";
+  if (c.max_slots < 1 || c.max_slots > 1024) return "max_slots out of range [1,1024]";
+  if (c.max_ctx < 32) return "max_ctx < 32";
+  if (c.prefill_chunk < 32) return "prefill_chunk < 32";
+  if (c.prefill_impl != 0 && c.prefill_impl != 1) return "prefill_impl must be 0 or 1";
+  if (c.weights_path) return "weights_path: loading checkpoints is not implemented; pass NULL for seeded random init";
+  return "";
+}
+
+int init_weights(llmc_engine* e) {
+  const ModelDims& d = e->d;
+  const int H = d.hidden, QD = d.qd(), KD = d.kd(), I = d.inter, V = d.vocab;
+  const size_t per_layer = (size_t)2 * H + (size_t)(QD + 2 * KD) * H + (size_t)H * QD + (size_t)2 * I * H + (size_t)H * I;
+  const size_t global = (size_t)V * H * (d.tied ? 1 : 2) + H;
+  e->wblob_elems = per_layer * d.layers + global;
+  if (int rc = dalloc(e, &e->wblob, e->wblob_elems)) return rc;
+  const float amp = (float)((double)d.init_std * 1.7320508075688772);
+  uint16_t* p = e->wblob;
+  auto take = [&](size_t n) { uint16_t* r = p; p += n; return r; };
+  cudaStream_t s = e->stream;
+  e->L.resize(d.layers);
+  for (int l = 0; l < d.layers; ++l) {
+    LayerW& w = e->L[l];
+    // matrices first so that every matrix start stays 16-byte aligned for any H % 8 == 0
+    w.wqkv = take((size_t)(QD + 2 * KD) * H);
+    w.wo = take((size_t)H * QD);
+    w.wgu = take((size_t)2 * I * H);
+    w.wd = take((size_t)H * I);
+    w.g1 = take(H);
+    w.g2 = take(H);
+    E_TRY(launch_init_gain(w.g1, H, e->seed, tensor_id(l, K_ATTN_NORM), s));
+    E_TRY(launch_init_matrix(w.wqkv, QD, H, H, e->seed, tensor_id(l, K_WQ), amp, 0, 0, s));
+    E_TRY(launch_init_matrix(w.wqkv, KD, H, H, e->seed, tensor_id(l, K_WK), amp, 0, QD, s));
+    E_TRY(launch_init_matrix(w.wqkv, KD, H, H, e->seed, tensor_id(l, K_WV), amp, 0, QD + KD, s));
+    E_TRY(launch_init_matrix(w.wo, H, QD, QD, e->seed, tensor_id(l, K_WO), amp, 0, 0, s));
+    E_TRY(launch_init_gain(w.g2, H, e->seed, tensor_id(l, K_MLP_NORM), s));
+    E_TRY(launch_init_matrix(w.wgu, I, H, H, e->seed, tensor_id(l, K_WG), amp, 1, 0, s));
+    E_TRY(launch_init_matrix(w.wgu, I, H, H, e->seed, tensor_id(l, K_WU), amp, 2, 0, s));
+    E_TRY(launch_init_matrix(w.wd, H, I, I, e->seed, tensor_id(l, K_WD), amp, 0, 0, s));
+  }
+  e->emb = take((size_t)V * H);
+  E_TRY(launch_init_matrix(e->emb, V, H, H, e->seed, tensor_id(-1, K_EMB), amp, 0, 0, s));
+  if (d.tied) {
+    e->lmhead = e->emb;
+  } else {
+    e->lmhead = take((size_t)V * H);
+    E_TRY(launch_init_matrix(e->lmhead, V, H, H, e->seed, tensor_id(-1, K_LMHEAD), amp, 0, 0, s));
+  }
+  e->gf = take(H);
+  E_TRY(launch_init_gain(e->gf, H, e->seed, tensor_id(-1, K_FINAL_NORM), s));
+  e->stats.kernel_launches += (uint64_t)d.layers * 9 + 3;
+  e->stats.weight_bytes = 2.0 * ((double)per_layer * d.layers + (double)V * H + H);
+  e->stats.kv_bytes_per_token = 2.0 * 2.0 * KD * d.layers;
+  return LLMC_OK;
+}
+
+int ensure_pages(llmc_engine* e, int slot, int need_tokens) {
+  if (need_tokens > e->max_ctx)
+    return fail(e, LLMC_ERR_LIMIT, "sequence would exceed max_ctx (" + std::to_string(e->max_ctx) + " tokens)");
+  const int need = (need_tokens + e->page_size - 1) / e->page_size;
+  int have = e->slot_npages[slot];
+  if (need <= have) return LLMC_OK;
+  if ((int)e->free_pages.size() < need - have) return fail(e, LLMC_ERR_OOM, "KV page pool exhausted");
+  int* row = &e->h_block_table[(size_t)slot * e->pages_per_seq];
+  for (int i = have; i < need; ++i) {
+    row[i] = e->free_pages.back();
+    e->free_pages.pop_back();
+  }
+  E_TRY(cudaMemcpyAsync(e->d_block_table + (size_t)slot * e->pages_per_seq + have, row + have,
+                        (size_t)(need - have) * sizeof(int), cudaMemcpyHostToDevice, e->stream));
+  e->slot_npages[slot] = need;
+  return LLMC_OK;
+}
+
+int gemm(llmc_engine* e, const uint16_t* A, const uint16_t* W, void* out, int T, int N, int K, int epi) {
+  if (e->prefill_impl == 0) E_TRY(launch_gemm_tcgen05(A, W, out, T, N, K, epi, e->stream));
+  else E_TRY(launch_gemm_simple(A, W, out, T, N, K, epi, e->stream));
+  e->stats.kernel_launches++;
+  return LLMC_OK;
+}
+
+GemvArgs base_args(llmc_engine* e, int B) {
+  GemvArgs a;
+  memset(&a, 0, sizeof(a));
+  const ModelDims& d = e->d;
+  a.B = B;
+  a.eps = d.rms_eps;
+  a.slots = e->d_slots;
+  a.next_token = e->d_next_token;
+  a.rope_cos = e->rope_cos;
+  a.rope_sin = e->rope_sin;
+  a.seq_len = e->d_seq_len;
+  a.block_table = e->d_block_table;
+  a.bt_stride = e->pages_per_seq;
+  a.page_size = e->page_size;
+  a.q_heads = d.q_heads;
+  a.kv_heads = d.kv_heads;
+  a.head_dim = d.head_dim;
+  return a;
+}
+
+int batch_tile(int B) { return B <= 1 ? 1 : (B <= 2 ? 2 : (B <= 4 ? 4 : 8)); }
+
+// LM head + greedy argmax over `B` rows of `xin`; finalises next_token / seq_len (+seq_inc)
+int lm_head(llmc_engine* e, const float* xin, int64_t x_stride, int B, const int* d_slots, float* logits, int seq_inc,
+            int* out_tokens, int* step_counter, bool pdl) {
+  GemvArgs a = base_args(e, B);
+  const ModelDims& d = e->d;
+  a.W = e->lmhead; a.N = d.vocab; a.K = d.hidden;
+  a.x = xin; a.x_stride = x_stride; a.gain = e->gf;
+  a.slots = d_slots;
+  a.y = logits; a.y_stride = d.vocab;
+  a.part_val = e->part_val; a.part_idx = e->part_idx; a.counter = e->lm_counter;
+  a.next_token_out = e->d_next_token; a.seq_len_out = e->d_seq_len; a.seq_inc = seq_inc;
+  a.out_tokens = out_tokens; a.out_stride = MAX_STEPS_PER_CALL; a.step_counter = step_counter;
+  E_TRY(launch_gemv(EPI_LMHEAD, PRO_NORM, batch_tile(B), a, pdl, e->stream));
+  e->stats.kernel_launches++;
+  return LLMC_OK;
+}
+
+// enqueue one decode step for the B sequences listed in d_slots
+int enqueue_decode_step(llmc_engine* e, int B, bool want_logits) {
+  const ModelDims& d = e->d;
+  const int H = d.hidden, QD = d.qd(), I = d.inter, bt = batch_tile(B);
+  const bool pdl = e->use_pdl;
+  const int nsplit = attn_decode_default_nsplit(B, d.kv_heads);
+  for (int l = 0; l < d.layers; ++l) {
+    const LayerW& w = e->L[l];
+    uint16_t* kp = e->kpool + (size_t)l * e->kv_layer_stride;
+    uint16_t* vp = e->vpool + (size_t)l * e->kv_layer_stride;
+    {  // RMSNorm -> QKV -> RoPE -> KV append   (layer 0 also gathers the embedding)
+      GemvArgs a = base_args(e, B);
+      a.W = w.wqkv; a.N = d.qkv_rows(); a.K = H;
+      a.x = e->x; a.x_stride = H; a.gain = w.g1;
+      a.emb = e->emb; a.x_out = e->x;
+      a.y = e->q; a.y_stride = QD;
+      a.kpool = kp; a.vpool = vp;
+      E_TRY(launch_gemv(EPI_QKV_ROPE, l == 0 ? PRO_EMBED_NORM : PRO_NORM, bt, a, pdl, e->stream));
+    }
+    {
+      AttnDecodeArgs a;
+      memset(&a, 0, sizeof(a));
+      a.q = e->q; a.out = e->attn; a.kpool = kp; a.vpool = vp;
+      a.slots = e->d_slots; a.seq_len = e->d_seq_len; a.ctx_extra = 1;
+      a.block_table = e->d_block_table; a.bt_stride = e->pages_per_seq;
+      a.page_size = e->page_size; a.q_heads = d.q_heads; a.kv_heads = d.kv_heads; a.head_dim = d.head_dim;
+      a.B = B; a.nsplit = nsplit; a.scratch = e->attn_scratch; a.counters = e->attn_counters;
+      E_TRY(launch_attn_decode(a, pdl, e->stream));
+    }
+    {  // x += Wo attn
+      GemvArgs a = base_args(e, B);
+      a.W = w.wo; a.N = H; a.K = QD;
+      a.x = e->attn; a.x_stride = QD;
+      a.y = e->x; a.y_stride = H;
+      E_TRY(launch_gemv(EPI_RESID, PRO_PLAIN, bt, a, pdl, e->stream));
+    }
+    {  // act = silu(Wg h) * (Wu h), h = RMSNorm(x)
+      GemvArgs a = base_args(e, B);
+      a.W = w.wgu; a.N = 2 * I; a.K = H;
+      a.x = e->x; a.x_stride = H; a.gain = w.g2;
+      a.y = e->act; a.y_stride = I;
+      E_TRY(launch_gemv(EPI_SWIGLU, PRO_NORM, bt, a, pdl, e->stream));
+    }
+    {  // x += Wd act
+      GemvArgs a = base_args(e, B);
+      a.W = w.wd; a.N = H; a.K = I;
+      a.x = e->act; a.x_stride = I;
+      a.y = e->x; a.y_stride = H;
+      E_TRY(launch_gemv(EPI_RESID, PRO_PLAIN, bt, a, pdl, e->stream));
+    }
+  }
+  e->stats.kernel_launches += (uint64_t)d.layers * 5;
+  return lm_head(e, e->x, H, B, e->d_slots, want_logits ? e->logits : nullptr, 1, e->d_out_tokens, e->d_step_counter,
+                 pdl);
+}
+
+int get_graph(llmc_engine* e, int B, bool want_logits, cudaGraphExec_t* out) {
+  const int key = B * 2 + (want_logits ? 1 : 0);
+  auto it = e->graphs.find(key);
+  if (it != e->graphs.end()) {
+    *out = it->second;
+    return LLMC_OK;
+  }
+  const uint64_t launches_before = e->stats.kernel_launches;
+  E_TRY(cudaStreamBeginCapture(e->stream, cudaStreamCaptureModeRelaxed));
+  int rc = enqueue_decode_step(e, B, want_logits);
+  cudaGraph_t g = nullptr;
+  cudaError_t ce = cudaStreamEndCapture(e->stream, &g);
+  e->stats.kernel_launches = launches_before;  // capture launched nothing
+  if (rc != LLMC_OK) {
+    if (g) cudaGraphDestroy(g);
+    return rc;
+  }
+  E_TRY(ce);
+  cudaGraphExec_t ge = nullptr;
+  ce = cudaGraphInstantiate(&ge, g, 0);
+  cudaGraphDestroy(g);
+  E_TRY(ce);
+  e->graphs[key] = ge;
+  *out = ge;
+  return LLMC_OK;
+}
+
+}  // namespace
+
+// ======================================================================== C ABI
+extern "C" {
+
+const char* llmc_version(void) { return "llmc 0.1 (sm_100a)"; }
+
+int llmc_device_count(void) {
+  int n = 0;
+  if (cudaGetDeviceCount(&n) != cudaSuccess) {
+    cudaGetLastError();
+    return 0;
+  }
+  return n;
+}
+
+const char* llmc_last_error(llmc_engine* e) { return e ? e->last_error.c_str() : g_create_error.c_str(); }
+
+void llmc_engine_destroy(llmc_engine* e) {
+  if (!e) return;
+  cudaSetDevice(e->device);
+  if (e->stream) cudaStreamSynchronize(e->stream);
+  for (auto& kv : e->graphs) cudaGraphExecDestroy(kv.second);
+  for (void* p : e->allocs) cudaFree(p);
+  if (e->ev0) cudaEventDestroy(e->ev0);
+  if (e->ev1) cudaEventDestroy(e->ev1);
+  if (e->stream) cudaStreamDestroy(e->stream);
+  delete e;
+}
+
+static int create_impl(llmc_engine* e, const llmc_config& c) {
+  E_TRY(cudaSetDevice(c.device));
+  E_TRY(cudaGetDeviceProperties(&e->prop, c.device));
+  if (e->prop.major != 10)
+    return fail(e, LLMC_ERR_CUDA, std::string("device ") + e->prop.name + " is compute capability " +
+                                      std::to_string(e->prop.major) + "." + std::to_string(e->prop.minor) +
+                                      "; this library contains sm_100a code only and has no fallback");
+  e->device = c.device;
+  e->d = ModelDims{c.hidden, c.layers, c.q_heads, c.kv_heads, c.head_dim, c.inter, c.vocab, c.tied,
+                   c.rope_theta, c.rms_eps, c.init_std};
+  e->seed = c.seed;
+  e->max_slots = c.max_slots; e->max_ctx = c.max_ctx; e->page_size = c.page_size;
+  e->prefill_chunk = c.prefill_chunk; e->prefill_impl = c.prefill_impl;
+  e->use_graph = !(c.flags & LLMC_FLAG_NO_GRAPH);
+  e->use_pdl = !(c.flags & LLMC_FLAG_NO_PDL);
+  e->stats.sm_count = e->prop.multiProcessorCount; e->stats.cc_major = e->prop.major; e->stats.cc_minor = e->prop.minor;
+  E_TRY(cudaStreamCreateWithFlags(&e->stream, cudaStreamNonBlocking));
+  E_TRY(cudaEventCreate(&e->ev0));
+  E_TRY(cudaEventCreate(&e->ev1));
+  if (int rc = init_weights(e)) return rc;
+
+  const ModelDims& d = e->d;
+  const int H = d.hidden, QD = d.qd(), KD = d.kd(), I = d.inter, V = d.vocab, D = d.head_dim;
+  const int MB = MAX_GEMV_BATCH;
+  // ---- KV pool: enough pages for every slot at max_ctx
+  e->pages_per_seq = (e->max_ctx + e->page_size - 1) / e->page_size;
+  e->num_pages = e->pages_per_seq * e->max_slots;
+  e->kv_layer_stride = (size_t)e->num_pages * KD * e->page_size;
+  if (int rc = dalloc(e, &e->kpool, e->kv_layer_stride * d.layers)) return rc;
+  if (int rc = dalloc(e, &e->vpool, e->kv_layer_stride * d.layers)) return rc;
+  if (int rc = dalloc(e, &e->d_block_table, (size_t)e->max_slots * e->pages_per_seq)) return rc;
+  E_TRY(cudaMemsetAsync(e->d_block_table, 0, (size_t)e->max_slots * e->pages_per_seq * sizeof(int), e->stream));
+  e->h_block_table.assign((size_t)e->max_slots * e->pages_per_seq, 0);
+  for (int p = e->num_pages - 1; p >= 0; --p) e->free_pages.push_back(p);
+  e->slot_npages.assign(e->max_slots, 0);
+  e->slot_used.assign(e->max_slots, 0);
+  e->h_seq_len.assign(e->max_slots, 0);
+  if (int rc = dalloc(e, &e->d_seq_len, e->max_slots)) return rc;
+  if (int rc = dalloc(e, &e->d_next_token, e->max_slots)) return rc;
+  E_TRY(cudaMemsetAsync(e->d_seq_len, 0, e->max_slots * sizeof(int), e->stream));
+  E_TRY(cudaMemsetAsync(e->d_next_token, 0, e->max_slots * sizeof(int), e->stream));
+  // ---- RoPE tables (double precision on the host, rounded once to fp32)
+  {
+    std::vector<float> hc((size_t)e->max_ctx * (D / 2)), hs((size_t)e->max_ctx * (D / 2));
+    for (int p = 0; p < e->max_ctx; ++p)
+      for (int i = 0; i < D / 2; ++i) {
+        const double inv = pow((double)d.rope_theta, -2.0 * i / (double)D);
+        const double a = (double)p * inv;
+        hc[(size_t)p * (D / 2) + i] = (float)cos(a);
+        hs[(size_t)p * (D / 2) + i] = (float)sin(a);
+      }
+    if (int rc = dalloc(e, &e->rope_cos, hc.size())) return rc;
+    if (int rc = dalloc(e, &e->rope_sin, hs.size())) return rc;
+    E_TRY(cudaMemcpy(e->rope_cos, hc.data(), hc.size() * 4, cudaMemcpyHostToDevice));
+    E_TRY(cudaMemcpy(e->rope_sin, hs.data(), hs.size() * 4, cudaMemcpyHostToDevice));
+  }
+  // ---- decode workspace
+  if (int rc = dalloc(e, &e->x, (size_t)MB * H)) return rc;
+  if (int rc = dalloc(e, &e->q, (size_t)MB * QD)) return rc;
+  if (int rc = dalloc(e, &e->attn, (size_t)MB * QD)) return rc;
+  if (int rc = dalloc(e, &e->act, (size_t)MB * I)) return rc;
+  if (int rc = dalloc(e, &e->logits, (size_t)MB * V)) return rc;
+  if (int rc = dalloc(e, &e->d_slots, MB)) return rc;
+  if (int rc = dalloc(e, &e->d_pslot, 1)) return rc;
+  const int lmb = gemv_lmhead_blocks(V);
+  if (int rc = dalloc(e, &e->part_val, (size_t)MB * lmb)) return rc;
+  if (int rc = dalloc(e, &e->part_idx, (size_t)MB * lmb)) return rc;
+  if (int rc = dalloc(e, &e->lm_counter, 1)) return rc;
+  if (int rc = dalloc(e, &e->attn_counters, (size_t)MB * d.kv_heads)) return rc;
+  size_t sc = 0;
+  for (int B = 1; B <= MB; ++B) {
+    size_t n = attn_decode_scratch_floats(B, d.q_heads, attn_decode_default_nsplit(B, d.kv_heads), D);
+    if (n > sc) sc = n;
+  }
+  if (int rc = dalloc(e, &e->attn_scratch, sc)) return rc;
+  if (int rc = dalloc(e, &e->d_out_tokens, (size_t)MB * MAX_STEPS_PER_CALL)) return rc;
+  if (int rc = dalloc(e, &e->d_step_counter, 1)) return rc;
+  if (int rc = dalloc(e, &e->d_dummy_counter, 1)) return rc;
+  E_TRY(cudaMemsetAsync(e->lm_counter, 0, sizeof(unsigned), e->stream));
+  E_TRY(cudaMemsetAsync(e->attn_counters, 0, (size_t)MB * d.kv_heads * sizeof(unsigned), e->stream));
+  E_TRY(cudaMemsetAsync(e->d_step_counter, 0, sizeof(int), e->stream));
+  E_TRY(cudaMemsetAsync(e->d_dummy_counter, 0, sizeof(int), e->stream));
+  // ---- prefill workspace
+  const int TC = e->prefill_chunk;
+  if (int rc = dalloc(e, &e->p_tokens, TC)) return rc;
+  if (int rc = dalloc(e, &e->px, (size_t)TC * H)) return rc;
+  if (int rc = dalloc(e, &e->pxn, (size_t)TC * H)) return rc;
+  if (int rc = dalloc(e, &e->pqkv, (size_t)TC * (QD + 2 * KD))) return rc;
+  if (int rc = dalloc(e, &e->pq, (size_t)TC * QD)) return rc;
+  if (int rc = dalloc(e, &e->pattn, (size_t)TC * QD)) return rc;
+  if (int rc = dalloc(e, &e->pact, (size_t)TC * I)) return rc;
+  E_TRY(cudaStreamSynchronize(e->stream));
+  E_TRY(cudaGetLastError());
+  e->stats.graph_enabled = e->use_graph;
+  e->stats.pdl_enabled = e->use_pdl;
+  return LLMC_OK;
+}
+
+int llmc_engine_create(const llmc_config* cfg, llmc_engine** out) {
+  if (!cfg || !out) return fail(nullptr, LLMC_ERR_INVALID, "null argument");
+  *out = nullptr;
+  llmc_config c = *cfg;
+  if (apply_shape(c) != LLMC_OK) return fail(nullptr, LLMC_ERR_INVALID, "unknown shape id");
+  if (c.rope_theta == 0.f) c.rope_theta = 500000.f;
+  if (c.rms_eps == 0.f) c.rms_eps = 1e-5f;
+  if (c.init_std == 0.f) c.init_std = 0.02f;
+  if (c.max_slots == 0) c.max_slots = 8;
+  if (c.max_ctx == 0) c.max_ctx = 8192;
+  if (c.page_size == 0) c.page_size = 64;
+  if (c.prefill_chunk == 0) c.prefill_chunk = 2048;
+  std::string v = validate(c);
+  if (!v.empty()) return fail(nullptr, LLMC_ERR_INVALID, v);
+  int ndev = llmc_device_count();
+  if (ndev <= 0) return fail(nullptr, LLMC_ERR_CUDA, "no CUDA device available; libllmc has no CPU fallback");
+  if (c.device < 0 || c.device >= ndev) return fail(nullptr, LLMC_ERR_INVALID, "device ordinal out of range");
+  llmc_engine* e = new llmc_engine();
+  int rc = create_impl(e, c);
+  if (rc != LLMC_OK) {
+    g_create_error = e->last_error;
+    llmc_engine_destroy(e);
+    return rc;
+  }
+  *out = e;
+  return LLMC_OK;
+}
+
+int llmc_seq_alloc(llmc_engine* e, int32_t* slot) {
+  if (!e || !slot) return LLMC_ERR_INVALID;
+  std::lock_guard<std::mutex> lk(e->mu);
+  for (int s = 0; s < e->max_slots; ++s)
+    if (!e->slot_used[s]) {
+      e->slot_used[s] = 1;
+      e->h_seq_len[s] = 0;
+      *slot = s;
+      return LLMC_OK;
+    }
+  return fail(e, LLMC_ERR_LIMIT, "all " + std::to_string(e->max_slots) + " sequence slots are in use");
+}
+
+static int check_slot(llmc_engine* e, int slot) {
+  if (slot < 0 || slot >= e->max_slots || !e->slot_used[slot])
+    return fail(e, LLMC_ERR_STATE, "slot " + std::to_string(slot) + " is not allocated");
+  return LLMC_OK;
+}
+
+int llmc_seq_free(llmc_engine* e, int32_t slot) {
+  if (!e) return LLMC_ERR_INVALID;
+  std::lock_guard<std::mutex> lk(e->mu);
+  if (int rc = check_slot(e, slot)) return rc;
+  E_TRY(cudaSetDevice(e->device));
+  E_TRY(cudaStreamSynchronize(e->stream));
+  int* row = &e->h_block_table[(size_t)slot * e->pages_per_seq];
+  for (int i = 0; i < e->slot_npages[slot]; ++i) e->free_pages.push_back(row[i]);
+  e->slot_npages[slot] = 0;
+  e->slot_used[slot] = 0;
+  e->h_seq_len[slot] = 0;
+  int zero = 0;
+  E_TRY(cudaMemcpyAsync(e->d_seq_len + slot, &zero, sizeof(int), cudaMemcpyHostToDevice, e->stream));
+  E_TRY(cudaStreamSynchronize(e->stream));
+  return LLMC_OK;
+}
+
+int llmc_seq_len(llmc_engine* e, int32_t slot, int32_t* len) {
+  if (!e || !len) return LLMC_ERR_INVALID;
+  std::lock_guard<std::mutex> lk(e->mu);
+  if (int rc = check_slot(e, slot)) return rc;
+  *len = e->h_seq_len[slot];
+  return LLMC_OK;
+}
+
+int llmc_seq_set_next_token(llmc_engine* e, int32_t slot, int32_t token) {
+  if (!e) return LLMC_ERR_INVALID;
+  std::lock_guard<std::mutex> lk(e->mu);
+  if (int rc = check_slot(e, slot)) return rc;
+  if (token < 0 || token >= e->d.vocab) return fail(e, LLMC_ERR_INVALID, "token id out of range");
+  E_TRY(cudaSetDevice(e->device));
+  E_TRY(cudaMemcpyAsync(e->d_next_token + slot, &token, sizeof(int), cudaMemcpyHostToDevice, e->stream));
+  E_TRY(cudaStreamSynchronize(e->stream));
+  return LLMC_OK;
+}
+
+int llmc_seq_get_next_token(llmc_engine* e, int32_t slot, int32_t* token) {
+  if (!e || !token) return LLMC_ERR_INVALID;
+  std::lock_guard<std::mutex> lk(e->mu);
+  if (int rc = check_slot(e, slot)) return rc;
+  E_TRY(cudaSetDevice(e->device));
+  E_TRY(cudaMemcpyAsync(token, e->d_next_token + slot, sizeof(int), cudaMemcpyDeviceToHost, e->stream));
+  E_TRY(cudaStreamSynchronize(e->stream));
+  return LLMC_OK;
+}
+
+int llmc_prefill(llmc_engine* e, int32_t slot, const int32_t* tokens, int32_t n, int32_t* next_token,
+                 float* logits_last) {
+  if (!e || !tokens || n < 1) return e ? fail(e, LLMC_ERR_INVALID, "llmc_prefill: null tokens or n < 1") : LLMC_ERR_INVALID;
+  std::lock_guard<std::mutex> lk(e->mu);
+  if (int rc = check_slot(e, slot)) return rc;
+  const ModelDims& d = e->d;
+  for (int i = 0; i < n; ++i)
+    if (tokens[i] < 0 || tokens[i] >= d.vocab) return fail(e, LLMC_ERR_INVALID, "token id out of range");
+  E_TRY(cudaSetDevice(e->device));
+  const int H = d.hidden, QD = d.qd(), KD = d.kd(), I = d.inter;
+  const int p_start = e->h_seq_len[slot];
+  if (int rc = ensure_pages(e, slot, p_start + n)) return rc;
+  cudaStream_t s = e->stream;
+  E_TRY(cudaEventRecord(e->ev0, s));
+  int last_tc = 0;
+  for (int c0 = 0; c0 < n; c0 += e->prefill_chunk) {
+    const int T = std::min(e->prefill_chunk, n - c0);
+    const int p0 = p_start + c0;
+    last_tc = T;
+    E_TRY(cudaMemcpyAsync(e->p_tokens, tokens + c0, (size_t)T * sizeof(int), cudaMemcpyHostToDevice, s));
+    E_TRY(launch_embed_rows(e->emb, e->p_tokens, T, H, e->px, s));
+    for (int l = 0; l < d.layers; ++l) {
+      const LayerW& w = e->L[l];
+      uint16_t* kp = e->kpool + (size_t)l * e->kv_layer_stride;
+      uint16_t* vp = e->vpool + (size_t)l * e->kv_layer_stride;
+      E_TRY(launch_rmsnorm_rows(e->px, w.g1, d.rms_eps, T, H, e->pxn, s));
+      if (int rc = gemm(e, e->pxn, w.wqkv, e->pqkv, T, QD + 2 * KD, H, GEMM_STORE_F32)) return rc;
+      E_TRY(launch_rope_append(e->pqkv, T, p0, slot, e->rope_cos, e->rope_sin, e->d_block_table, e->pages_per_seq,
+                               kp, vp, e->page_size, d.q_heads, d.kv_heads, d.head_dim, e->pq, s));
+      E_TRY(launch_prefill_attention(e->pq, T, p0, slot, e->d_block_table, e->pages_per_seq, kp, vp, e->page_size,
+                                     d.q_heads, d.kv_heads, d.head_dim, e->pattn, s));
+      if (int rc = gemm(e, e->pattn, w.wo, e->px, T, H, QD, GEMM_RESID_F32)) return rc;
+      E_TRY(launch_rmsnorm_rows(e->px, w.g2, d.rms_eps, T, H, e->pxn, s));
+      if (int rc = gemm(e, e->pxn, w.wgu, e->pact, T, 2 * I, H, GEMM_SWIGLU_BF16)) return rc;
+      if (int rc = gemm(e, e->pact, w.wd, e->px, T, H, I, GEMM_RESID_F32)) return rc;
+    }
+    e->stats.kernel_launches += 1 + (uint64_t)d.layers * 4;
+  }
+  // the cache now holds p_start + n tokens; LM head + argmax on the last row
+  const int new_len = p_start + n;
+  E_TRY(cudaMemcpyAsync(e->d_seq_len + slot, &new_len, sizeof(int), cudaMemcpyHostToDevice, s));
+  int hslot = slot;
+  E_TRY(cudaMemcpyAsync(e->d_pslot, &hslot, sizeof(int), cudaMemcpyHostToDevice, s));
+  if (int rc = lm_head(e, e->px + (size_t)(last_tc - 1) * H, H, 1, e->d_pslot, logits_last ? e->logits : nullptr, 0,
+                       nullptr, e->d_dummy_counter, false))
+    return rc;
+  E_TRY(cudaEventRecord(e->ev1, s));
+  int tok = -1;
+  E_TRY(cudaMemcpyAsync(&tok, e->d_next_token + slot, sizeof(int), cudaMemcpyDeviceToHost, s));
+  if (logits_last)
+    E_TRY(cudaMemcpyAsync(logits_last, e->logits, (size_t)d.vocab * sizeof(float), cudaMemcpyDeviceToHost, s));
+  E_TRY(cudaStreamSynchronize(s));
+  E_TRY(cudaGetLastError());
+  e->h_seq_len[slot] = new_len;
+  if (next_token) *next_token = tok;
+  e->stats.prefill_tokens += n;
+  cudaEventElapsedTime(&e->stats.last_prefill_ms, e->ev0, e->ev1);
+  return LLMC_OK;
+}
+
+int llmc_decode(llmc_engine* e, const int32_t* slots, int32_t nslots, int32_t nsteps, int32_t* out_tokens,
+                float* logits) {
+  if (!e || !slots) return e ? fail(e, LLMC_ERR_INVALID, "llmc_decode: null slots") : LLMC_ERR_INVALID;
+  std::lock_guard<std::mutex> lk(e->mu);
+  if (nslots < 1 || nslots > MAX_GEMV_BATCH)
+    return fail(e, LLMC_ERR_LIMIT, "llmc_decode: nslots must be in [1," + std::to_string(MAX_GEMV_BATCH) + "]");
+  if (nsteps < 1 || nsteps > MAX_STEPS_PER_CALL)
+    return fail(e, LLMC_ERR_LIMIT, "llmc_decode: nsteps must be in [1," + std::to_string(MAX_STEPS_PER_CALL) + "]");
+  for (int i = 0; i < nslots; ++i) {
+    if (int rc = check_slot(e, slots[i])) return rc;
+    if (e->h_seq_len[slots[i]] < 1) return fail(e, LLMC_ERR_STATE, "llmc_decode: slot has no prefilled tokens");
+    for (int j = 0; j < i; ++j)
+      if (slots[j] == slots[i]) return fail(e, LLMC_ERR_INVALID, "llmc_decode: duplicate slot");
+  }
+  E_TRY(cudaSetDevice(e->device));
+  for (int i = 0; i < nslots; ++i)
+    if (int rc = ensure_pages(e, slots[i], e->h_seq_len[slots[i]] + nsteps)) return rc;
+  cudaStream_t s = e->stream;
+  const ModelDims& d = e->d;
+  E_TRY(cudaMemcpyAsync(e->d_slots, slots, (size_t)nslots * sizeof(int), cudaMemcpyHostToDevice, s));
+  E_TRY(cudaMemsetAsync(e->d_step_counter, 0, sizeof(int), s));
+  const bool want_logits = logits != nullptr;
+  cudaGraphExec_t ge = nullptr;
+  if (e->use_graph) {
+    int rc = get_graph(e, nslots, want_logits, &ge);
+    if (rc != LLMC_OK) return rc;
+  }
+  E_TRY(cudaEventRecord(e->ev0, s));
+  for (int st = 0; st < nsteps; ++st) {
+    if (ge) {
+      E_TRY(cudaGraphLaunch(ge, s));
+      e->stats.kernel_launches += (uint64_t)d.layers * 5 + 1;
+    } else {
+      if (int rc = enqueue_decode_step(e, nslots, want_logits)) return rc;
+    }
+  }
+  E_TRY(cudaEventRecord(e->ev1, s));
+  std::vector<int> host((size_t)nslots * nsteps);
+  for (int i = 0; i < nslots; ++i)
+    E_TRY(cudaMemcpyAsync(host.data() + (size_t)i * nsteps, e->d_out_tokens + (size_t)i * MAX_STEPS_PER_CALL,
+                          (size_t)nsteps * sizeof(int), cudaMemcpyDeviceToHost, s));
+  if (want_logits)
+    E_TRY(cudaMemcpyAsync(logits, e->logits, (size_t)nslots * d.vocab * sizeof(float), cudaMemcpyDeviceToHost, s));
+  E_TRY(cudaStreamSynchronize(s));
+  E_TRY(cudaGetLastError());
+  if (out_tokens) memcpy(out_tokens, host.data(), host.size() * sizeof(int));
+  for (int i = 0; i < nslots; ++i) e->h_seq_len[slots[i]] += nsteps;
+  e->stats.decode_steps += nsteps;
+  cudaEventElapsedTime(&e->stats.last_decode_ms, e->ev0, e->ev1);
+  return LLMC_OK;
+}
+
+int llmc_engine_stats(llmc_engine* e, llmc_stats* out) {
+  if (!e || !out) return LLMC_ERR_INVALID;
+  std::lock_guard<std::mutex> lk(e->mu);
+  *out = e->stats;
+  return LLMC_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,63 @@
+// engine_internal.h -- the engine object behind the opaque llmc_engine handle.
+#pragma once
+#include <cuda_runtime.h>
+#include <map>
+#include <mutex>
+#include <string>
+#include <vector>
+#include "../../include/llmc.h"
+#include "common.cuh"
+#include "kernels.h"
+
+namespace llmc {
+constexpr int MAX_STEPS_PER_CALL = 4096;
+struct LayerW {
+  uint16_t *g1, *wqkv, *wo, *g2, *wgu, *wd;
+};
+}  // namespace llmc
+
+struct llmc_engine {
+  int device = 0;
+  llmc::ModelDims d{};
+  uint64_t seed = 0;
+  int max_slots = 8, max_ctx = 8192, page_size = 64, prefill_chunk = 2048, prefill_impl = 0;
+  bool use_graph = true, use_pdl = true;
+  int pages_per_seq = 0, num_pages = 0;
+  cudaStream_t stream = nullptr;
+  cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+  cudaDeviceProp prop{};
+  // weights
+  uint16_t* wblob = nullptr;
+  size_t wblob_elems = 0;
+  std::vector<llmc::LayerW> L;
+  uint16_t *emb = nullptr, *lmhead = nullptr, *gf = nullptr;
+  // kv
+  uint16_t *kpool = nullptr, *vpool = nullptr;
+  size_t kv_layer_stride = 0;
+  int* d_block_table = nullptr;
+  std::vector<int> h_block_table;
+  std::vector<int> free_pages;
+  std::vector<int> slot_npages;
+  std::vector<char> slot_used;
+  std::vector<int> h_seq_len;
+  int *d_seq_len = nullptr, *d_next_token = nullptr;
+  float *rope_cos = nullptr, *rope_sin = nullptr;
+  // decode workspace
+  float *x = nullptr, *q = nullptr, *attn = nullptr, *act = nullptr, *logits = nullptr;
+  int* d_slots = nullptr;
+  float* part_val = nullptr;
+  int* part_idx = nullptr;
+  unsigned *lm_counter = nullptr, *attn_counters = nullptr;
+  float* attn_scratch = nullptr;
+  int *d_out_tokens = nullptr, *d_step_counter = nullptr, *d_dummy_counter = nullptr, *d_pslot = nullptr;
+  // prefill workspace
+  int* p_tokens = nullptr;
+  float *px = nullptr, *pqkv = nullptr;
+  uint16_t *pxn = nullptr, *pq = nullptr, *pattn = nullptr, *pact = nullptr;
+  std::map<int, cudaGraphExec_t> graphs;  // key = B * 2 + want_logits
+  std::mutex mu;
+  std::string last_error;
+  llmc_stats stats{};
+  std::vector<void*> allocs;
+};
+

@@ -1,0 +1,320 @@
+// gemm_tcgen05.cu -- the prefill GEMM on the 5th-generation tensor cores (sm_100a):
+//   C[T][N] = A[T][K] * W[N][K]^T,  bf16 operands, fp32 accumulation in TMEM.
+//
+// Tensor-pipe bound (2*T*N*K flops per call).  One CTA per 128 x BN output
+// tile, warp-specialised:
+//   warp 0      TMA producer: cp.async.bulk.tensor 2-D loads of a 128x64 A tile and a BNx64 W
+//               tile per k-step into a 128B-swizzled shared-memory ring (mbarrier full/empty)
+//   warp 1      allocates TMEM; one elected lane issues tcgen05.mma (M=128, N=BN, K=16 per
+//               instruction, 4 per k-step) with shared-memory operand descriptors; commits
+//               release the ring slots and finally signal the epilogue
+//   warps 2-5   epilogue: tcgen05.ld the accumulator (each warp its own TMEM lane quadrant),
+//               apply the fused epilogue (bf16/f32 store, residual add, SwiGLU) and store
+// Both operands are K-major, so W is used exactly as the decode GEMV streams it.
+//
+// No counterpart in the reference (/root/reference/internal/provider/provider.go:13-21 is the
+// boundary; the providers behind it are remote HTTP calls).
+#include <cuda.h>
+#include <mutex>
+#include "common.cuh"
+#include "kernels.h"
+
+namespace llmc {
+
+namespace {
+
+constexpr int BM = 128, BK = 64, UMMA_K = 16;
+constexpr int GEMM_THREADS = 192;
+
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+  asm volatile(
+      "{\n\t"
+      ".reg .pred p;\n\t"
+      "WAIT_LOOP:\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+      "@p bra WAIT_DONE;\n\t"
+      "bra WAIT_LOOP;\n\t"
+      "WAIT_DONE:\n\t"
+      "}" ::"r"(bar), "r"(parity)
+      : "memory");
+}
+__device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap* map, int c0, int c1, uint32_t bar) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];" ::"r"(dst),
+      "l"(map), "r"(bar), "r"(c0), "r"(c1)
+      : "memory");
+}
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_commit(uint32_t bar) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void tc_mma_bf16(uint32_t tmem_d, uint64_t da, uint64_t db, uint32_t idesc, uint32_t acc) {
+  asm volatile(
+      "{\n\t"
+      ".reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t"
+      "}" ::"r"(tmem_d),
+      "l"(da), "l"(db), "r"(idesc), "r"(acc)
+      : "memory");
+}
+__device__ __forceinline__ void tc_ld32(uint32_t taddr, uint32_t (&r)[32]) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+      "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+      "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
+        "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]), "=r"(r[16]),
+        "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]), "=r"(r[24]),
+        "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+      : "r"(taddr));
+}
+__device__ __forceinline__ void tc_wait_ld() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
+
+// shared-memory operand descriptor: K-major tile of [rows][64] bf16 written by TMA with 128B
+// swizzle -- 8-row groups 1024 B apart (SBO), LBO unused (1), descriptor version 1, SWIZZLE_128B
+__device__ __forceinline__ uint64_t make_smem_desc(uint32_t addr) {
+  return (uint64_t)((addr & 0x3FFFFu) >> 4) | (1ull << 16) | ((uint64_t)(1024 >> 4) << 32) | (1ull << 46) |
+         (2ull << 61);
+}
+// instruction descriptor, kind::f16: D fp32, A/B bf16, both K-major, M=128, N
+__host__ __device__ constexpr uint32_t make_idesc(int n) {
+  return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(n >> 3) << 17) | ((uint32_t)(BM >> 4) << 24);
+}
+
+template <int BN>
+struct TileCfg {
+  static constexpr int STAGES = BN == 256 ? 4 : 6;
+  static constexpr int A_BYTES = BM * BK * 2;
+  static constexpr int B_BYTES = BN * BK * 2;
+  static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
+  static constexpr int SMEM = STAGES * STAGE_BYTES + 1024 /*alignment slack*/ + 256 /*barriers*/;
+};
+
+template <int BN, int EPI>
+__global__ void __launch_bounds__(GEMM_THREADS, 1)
+    gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmW,
+                   void* __restrict__ out, int T, int N, int K) {
+  using C = TileCfg<BN>;
+  extern __shared__ unsigned char smem_raw[];
+  const uint32_t raw = smem_u32(smem_raw);
+  const uint32_t base = (raw + 1023u) & ~1023u;  // SWIZZLE_128B operands need 1024-byte alignment
+  unsigned char* base_ptr = smem_raw + (base - raw);
+  const uint32_t bar_base = base + C::STAGES * C::STAGE_BYTES;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(base_ptr + C::STAGES * C::STAGE_BYTES + 128);
+  auto full_bar = [&](int s) { return bar_base + 8u * s; };
+  auto empty_bar = [&](int s) { return bar_base + 8u * (C::STAGES + s); };
+  const uint32_t tmem_full_bar = bar_base + 8u * (2 * C::STAGES);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int n0 = blockIdx.x * BN, m0 = blockIdx.y * BM;
+  const int KB = K / BK;
+
+  if (threadIdx.x == 0) {
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&tmA) : "memory");
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&tmW) : "memory");
+    for (int s = 0; s < C::STAGES; ++s) {
+      mbar_init(full_bar(s), 1);
+      mbar_init(empty_bar(s), 1);
+    }
+    mbar_init(tmem_full_bar, 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 1) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)),
+                 "r"((uint32_t)BN)
+                 : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *reinterpret_cast<volatile uint32_t*>(tmem_slot);
+
+  if (warp == 0) {
+    if (lane == 0) {
+      for (int kb = 0; kb < KB; ++kb) {
+        const int s = kb % C::STAGES;
+        const uint32_t ph = (kb / C::STAGES) & 1;
+        mbar_wait(empty_bar(s), ph ^ 1u);
+        mbar_expect_tx(full_bar(s), C::STAGE_BYTES);
+        const uint32_t sa = base + s * C::STAGE_BYTES;
+        tma_load_2d(sa, &tmA, kb * BK, m0, full_bar(s));
+        tma_load_2d(sa + C::A_BYTES, &tmW, kb * BK, n0, full_bar(s));
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {
+      constexpr uint32_t idesc = make_idesc(BN);
+      for (int kb = 0; kb < KB; ++kb) {
+        const int s = kb % C::STAGES;
+        const uint32_t ph = (kb / C::STAGES) & 1;
+        mbar_wait(full_bar(s), ph);
+        tc_fence_after();
+        const uint32_t sa = base + s * C::STAGE_BYTES;
+        const uint32_t sb = sa + C::A_BYTES;
+#pragma unroll
+        for (int k = 0; k < BK / UMMA_K; ++k) {
+          const uint64_t da = make_smem_desc(sa + k * UMMA_K * 2);
+          const uint64_t db = make_smem_desc(sb + k * UMMA_K * 2);
+          tc_mma_bf16(tmem_base, da, db, idesc, (kb | k) != 0 ? 1u : 0u);
+        }
+        tc_commit(empty_bar(s));  // slot reusable once these MMAs have read it
+      }
+      tc_commit(tmem_full_bar);   // accumulator complete
+    }
+  } else {
+    // ---- epilogue: warp w may only touch TMEM lanes [32*(w%4), +32)
+    const int quad = warp & 3;
+    const int row = m0 + quad * 32 + lane;
+    mbar_wait(tmem_full_bar, 0);
+    tc_fence_after();
+    const uint32_t tq = tmem_base + ((uint32_t)(quad * 32) << 16);
+    if (EPI == GEMM_SWIGLU_BF16) {
+      uint16_t* o = reinterpret_cast<uint16_t*>(out) + (size_t)row * (N / 2) + n0 / 2;
+#pragma unroll 1
+      for (int blk = 0; blk < BN / 128; ++blk)
+#pragma unroll 1
+        for (int half = 0; half < 2; ++half) {
+          uint32_t g[32], u[32];
+          tc_ld32(tq + blk * 128 + half * 32, g);
+          tc_ld32(tq + blk * 128 + 64 + half * 32, u);
+          tc_wait_ld();
+          if (row < T) {
+            uint32_t pk[16];
+#pragma unroll
+            for (int i = 0; i < 16; ++i) {
+              const float g0 = __uint_as_float(g[2 * i]), g1 = __uint_as_float(g[2 * i + 1]);
+              const float a0 = g0 / (1.0f + __expf(-g0)) * __uint_as_float(u[2 * i]);
+              const float a1 = g1 / (1.0f + __expf(-g1)) * __uint_as_float(u[2 * i + 1]);
+              pk[i] = pack_bf16x2(a0, a1);
+            }
+            uint4* dst = reinterpret_cast<uint4*>(o + blk * 64 + half * 32);
+#pragma unroll
+            for (int i = 0; i < 4; ++i) dst[i] = make_uint4(pk[4 * i], pk[4 * i + 1], pk[4 * i + 2], pk[4 * i + 3]);
+          }
+        }
+    } else {
+#pragma unroll 1
+      for (int c = 0; c < BN / 32; ++c) {
+        uint32_t v[32];
+        tc_ld32(tq + c * 32, v);
+        tc_wait_ld();
+        if (row < T) {
+          const size_t off = (size_t)row * N + n0 + c * 32;
+          if (EPI == GEMM_STORE_BF16) {
+            uint4* dst = reinterpret_cast<uint4*>(reinterpret_cast<uint16_t*>(out) + off);
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+              uint32_t pk[4];
+#pragma unroll
+              for (int j = 0; j < 4; ++j)
+                pk[j] = pack_bf16x2(__uint_as_float(v[8 * i + 2 * j]), __uint_as_float(v[8 * i + 2 * j + 1]));
+              dst[i] = make_uint4(pk[0], pk[1], pk[2], pk[3]);
+            }
+          } else {
+            float4* dst = reinterpret_cast<float4*>(reinterpret_cast<float*>(out) + off);
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+              float4 r = make_float4(__uint_as_float(v[4 * i]), __uint_as_float(v[4 * i + 1]),
+                                     __uint_as_float(v[4 * i + 2]), __uint_as_float(v[4 * i + 3]));
+              if (EPI == GEMM_RESID_F32) {
+                const float4 old = dst[i];
+                r.x += old.x; r.y += old.y; r.z += old.z; r.w += old.w;
+              }
+              dst[i] = r;
+            }
+          }
+        }
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"((uint32_t)BN) : "memory");
+  }
+}
+
+// ---- host side: tensor maps through the driver entry point (no link-time libcuda dependency)
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+EncodeTiledFn get_encode() {
+  static EncodeTiledFn fn = nullptr;
+  static std::once_flag once;
+  std::call_once(once, [] {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess &&
+        q == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<EncodeTiledFn>(p);
+  });
+  return fn;
+}
+
+// 2-D bf16 row-major [rows][cols] tensor, box = [box_rows][64], 128B swizzle
+bool make_map(CUtensorMap* m, const void* ptr, uint64_t rows, uint64_t cols, uint32_t box_rows) {
+  EncodeTiledFn enc = get_encode();
+  if (!enc) return false;
+  cuuint64_t dims[2] = {cols, rows};
+  cuuint64_t strides[1] = {cols * 2};
+  cuuint32_t box[2] = {(cuuint32_t)BK, box_rows};
+  cuuint32_t estr[2] = {1, 1};
+  return enc(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(ptr), dims, strides, box, estr,
+             CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+             CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+}
+
+template <int BN, int EPI>
+cudaError_t launch_tile(const uint16_t* A, const uint16_t* W, void* out, int T, int N, int K, cudaStream_t s) {
+  CUtensorMap ma, mw;
+  if (!make_map(&ma, A, (uint64_t)T, (uint64_t)K, BM) || !make_map(&mw, W, (uint64_t)N, (uint64_t)K, BN))
+    return cudaErrorInvalidValue;
+  auto kern = gemm_tc_kernel<BN, EPI>;
+  cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, TileCfg<BN>::SMEM);
+  if (e != cudaSuccess) return e;
+  dim3 grid(N / BN, (T + BM - 1) / BM);
+  kern<<<grid, GEMM_THREADS, TileCfg<BN>::SMEM, s>>>(ma, mw, out, T, N, K);
+  return cudaGetLastError();
+}
+
+template <int EPI>
+cudaError_t launch_epi(const uint16_t* A, const uint16_t* W, void* out, int T, int N, int K, cudaStream_t s) {
+  // pick the widest tile that still yields at least ~one wave of CTAs on 148 SMs
+  const int mt = (T + BM - 1) / BM;
+  if (N % 256 == 0 && (N / 256) * mt >= 148) return launch_tile<256, EPI>(A, W, out, T, N, K, s);
+  if (EPI == GEMM_SWIGLU_BF16) {
+    if (N % 128 != 0) return cudaErrorInvalidValue;
+    return launch_tile<128, EPI>(A, W, out, T, N, K, s);
+  }
+  if (N % 128 == 0 && (N / 128) * mt >= 148) return launch_tile<128, EPI>(A, W, out, T, N, K, s);
+  return launch_tile<64, EPI>(A, W, out, T, N, K, s);
+}
+
+}  // namespace
+
+cudaError_t launch_gemm_tcgen05(const uint16_t* A, const uint16_t* W, void* out, int T, int N, int K, int epi,
+                                cudaStream_t s) {
+  if (K % BK != 0 || T < 1 || N % 64 != 0) return cudaErrorInvalidValue;
+  switch (epi) {
+    case GEMM_STORE_BF16: return launch_epi<GEMM_STORE_BF16>(A, W, out, T, N, K, s);
+    case GEMM_STORE_F32: return launch_epi<GEMM_STORE_F32>(A, W, out, T, N, K, s);
+    case GEMM_RESID_F32: return launch_epi<GEMM_RESID_F32>(A, W, out, T, N, K, s);
+    case GEMM_SWIGLU_BF16: return launch_epi<GEMM_SWIGLU_BF16>(A, W, out, T, N, K, s);
+  }
+  return cudaErrorInvalidValue;
+}
+
+}  // namespace llmc

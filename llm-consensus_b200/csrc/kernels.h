@@ -1,0 +1,109 @@
+// kernels.h -- launch interfaces of the sm_100a kernels (internal to libllmc.so).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace llmc {
+
+// ------------------------------------------------------------------ init.cu
+cudaError_t launch_init_matrix(uint16_t* dst, int64_t rows, int cols, int64_t ld, uint64_t seed, uint32_t tid,
+                               float amp, int mode, int64_t row_off, cudaStream_t s);
+cudaError_t launch_init_gain(uint16_t* dst, int n, uint64_t seed, uint32_t tid, cudaStream_t s);
+
+// ------------------------------------------------------------------ gemv.cu (decode)
+enum GemvPro { PRO_PLAIN = 0, PRO_NORM = 1, PRO_EMBED_NORM = 2 };
+enum GemvEpi { EPI_STORE = 0, EPI_RESID = 1, EPI_QKV_ROPE = 2, EPI_SWIGLU = 3, EPI_LMHEAD = 4 };
+
+constexpr int MAX_GEMV_BATCH = 8;
+
+struct GemvArgs {
+  // weights, packed [N][K] bf16, row-major, K % 256 == 0
+  const uint16_t* W;
+  int N, K;
+  int B;  // live batch rows
+  // ---- prologue
+  const float* x;         // [B][x_stride] fp32 activations (PRO_PLAIN, PRO_NORM)
+  int64_t x_stride;
+  const uint16_t* gain;   // [K] bf16 RMSNorm gain (PRO_NORM, PRO_EMBED_NORM)
+  float eps;
+  const uint16_t* emb;    // [V][K] (PRO_EMBED_NORM): x[b] = emb[next_token[slots[b]]]
+  const int* slots;       // [B] sequence slot of batch row b
+  const int* next_token;  // [max_slots]
+  float* x_out;           // [B][K] residual stream written by block 0 (PRO_EMBED_NORM)
+  // ---- epilogue
+  float* y;               // STORE: y[b][n]; RESID: y[b][n] += ; SWIGLU: act[b][j]; LMHEAD: logits (nullable)
+  int64_t y_stride;
+  // QKV_ROPE
+  const float* rope_cos;  // [max_ctx][head_dim/2]
+  const float* rope_sin;
+  const int* seq_len;     // [max_slots] tokens already in the cache = position of the new token
+  const int* block_table; // [max_slots][bt_stride] page ids
+  int bt_stride;
+  uint16_t* kpool;        // this layer's K pages [page][kv_head][page_size][head_dim]
+  uint16_t* vpool;
+  int page_size, q_heads, kv_heads, head_dim;
+  // LMHEAD (greedy argmax, lowest index wins ties; last block finalises the step)
+  float* part_val;        // [B][gridDim.x]
+  int* part_idx;
+  unsigned* counter;      // zero on entry, left zero on exit
+  int* next_token_out;    // [max_slots]
+  int* seq_len_out;       // [max_slots], += seq_inc
+  int seq_inc;
+  int* out_tokens;        // [B][out_stride], written at column *step_counter
+  int out_stride;
+  int* step_counter;      // incremented once per launch
+};
+
+// Launch one fused GEMV.  `bt` is the compiled batch tile (1, 2, 4 or 8 >= args.B).
+cudaError_t launch_gemv(int epi, int pro, int bt, const GemvArgs& a, bool pdl, cudaStream_t s);
+// upper bound of blocks launch_gemv uses for an LM head of N rows (sizes part_val/part_idx)
+int gemv_lmhead_blocks(int N);
+
+// ------------------------------------------------------------------ attn_decode.cu
+struct AttnDecodeArgs {
+  const float* q;          // [B][q_heads*head_dim] fp32 (RoPE applied)
+  float* out;              // [B][q_heads*head_dim] fp32
+  const uint16_t* kpool;   // this layer's pages [page][kv_head][page_size][head_dim] bf16
+  const uint16_t* vpool;
+  const int* slots;        // [B]
+  const int* seq_len;      // [max_slots]; context length used = seq_len + ctx_extra
+  int ctx_extra;           // 1 during decode (the token appended by this step's QKV kernel)
+  const int* block_table;
+  int bt_stride;
+  int page_size, q_heads, kv_heads, head_dim;
+  int B, nsplit;
+  float* scratch;          // [B][q_heads][nsplit][head_dim + 2] split partials (o, m, l)
+  unsigned* counters;      // [B][kv_heads], zero on entry, left zero on exit
+};
+cudaError_t launch_attn_decode(const AttnDecodeArgs& a, bool pdl, cudaStream_t s);
+size_t attn_decode_scratch_floats(int B, int q_heads, int nsplit, int head_dim);
+int attn_decode_default_nsplit(int B, int kv_heads);
+
+// ------------------------------------------------------------------ prefill.cu
+cudaError_t launch_embed_rows(const uint16_t* emb, const int* tokens, int T, int H, float* x, cudaStream_t s);
+cudaError_t launch_rmsnorm_rows(const float* x, const uint16_t* gain, float eps, int T, int H, uint16_t* out_bf16,
+                                cudaStream_t s);
+// qkv fp32 [T][qd+2kd] -> q bf16 [T][qd] (RoPE), k/v appended to the pages at positions p0..p0+T-1
+cudaError_t launch_rope_append(const float* qkv, int T, int p0, int slot, const float* rope_cos,
+                               const float* rope_sin, const int* block_table, int bt_stride, uint16_t* kpool,
+                               uint16_t* vpool, int page_size, int q_heads, int kv_heads, int head_dim,
+                               uint16_t* q_out, cudaStream_t s);
+// causal attention of T new rows (positions p0..p0+T-1) over the paged cache; out bf16 [T][qd]
+cudaError_t launch_prefill_attention(const uint16_t* q, int T, int p0, int slot, const int* block_table,
+                                     int bt_stride, const uint16_t* kpool, const uint16_t* vpool, int page_size,
+                                     int q_heads, int kv_heads, int head_dim, uint16_t* out, cudaStream_t s);
+
+// ------------------------------------------------------------------ gemm_tcgen05.cu / gemm_simple.cu (prefill)
+// C[T][N] = A[T][K] (bf16) * W[N][K]^T (bf16), fp32 accumulation.
+enum GemmEpi {
+  GEMM_STORE_BF16 = 0,  // out bf16 [T][N]
+  GEMM_STORE_F32 = 1,   // out f32  [T][N]
+  GEMM_RESID_F32 = 2,   // out f32  [T][N] += acc
+  GEMM_SWIGLU_BF16 = 3  // W rows gate/up interleaved in blocks of 64; out bf16 [T][N/2] = silu(g)*u
+};
+cudaError_t launch_gemm_tcgen05(const uint16_t* A, const uint16_t* W, void* out, int T, int N, int K, int epi,
+                                cudaStream_t s);
+cudaError_t launch_gemm_simple(const uint16_t* A, const uint16_t* W, void* out, int T, int N, int K, int epi,
+                               cudaStream_t s);
+
+}  // namespace llmc

@@ -1,0 +1,229 @@
+// prefill.cu -- the row-wise kernels around the prefill GEMMs: embedding gather, RMSNorm
+// (fp32 residual stream -> bf16 GEMM operand), RoPE + paged-KV append, causal attention.
+//
+// All are HBM/L2-bound elementwise or reduction kernels except the attention, which is the
+// first (CUDA-core, shared-memory tiled) version: one warp per query row, the q heads of a
+// GQA group served from one staged K/V tile.
+//
+// No counterpart in the reference (/root/reference/internal/provider/provider.go:13-21 is the
+// boundary; the providers behind it are remote HTTP calls).
+#include "common.cuh"
+#include "kernels.h"
+#include "attn_common.cuh"
+
+namespace llmc {
+
+namespace {
+
+__global__ void __launch_bounds__(256) embed_rows_kernel(const uint16_t* __restrict__ emb, const int* __restrict__ tokens,
+                                                         int T, int H, float* __restrict__ x) {
+  const int t = blockIdx.x;
+  const int tok = tokens[t];
+  const uint16_t* e = emb + (size_t)tok * H;
+  float* xr = x + (size_t)t * H;
+  for (int k = threadIdx.x * 8; k < H; k += blockDim.x * 8) {
+    uint4 w = *reinterpret_cast<const uint4*>(e + k);
+    *reinterpret_cast<float4*>(xr + k) = make_float4(bf16lo(w.x), bf16hi(w.x), bf16lo(w.y), bf16hi(w.y));
+    *reinterpret_cast<float4*>(xr + k + 4) = make_float4(bf16lo(w.z), bf16hi(w.z), bf16lo(w.w), bf16hi(w.w));
+  }
+}
+
+// one block (256 threads) per row; two passes over a row that stays in L1/L2
+__global__ void __launch_bounds__(256) rmsnorm_rows_kernel(const float* __restrict__ x, const uint16_t* __restrict__ gain,
+                                                           float eps, int T, int H, uint16_t* __restrict__ out) {
+  __shared__ float red[8];
+  const int t = blockIdx.x, tid = threadIdx.x;
+  const float* xr = x + (size_t)t * H;
+  float ss = 0.f;
+  for (int k = tid * 4; k < H; k += 256 * 4) {
+    float4 v = *reinterpret_cast<const float4*>(xr + k);
+    ss += v.x * v.x + v.y * v.y + v.z * v.z + v.w * v.w;
+  }
+  ss = warp_sum(ss);
+  if ((tid & 31) == 0) red[tid >> 5] = ss;
+  __syncthreads();
+  float tot = 0.f;
+#pragma unroll
+  for (int w = 0; w < 8; ++w) tot += red[w];
+  const float r = rsqrtf(tot / (float)H + eps);
+  for (int k = tid * 4; k < H; k += 256 * 4) {
+    float4 v = *reinterpret_cast<const float4*>(xr + k);
+    uint2 g = *reinterpret_cast<const uint2*>(gain + k);
+    uint2 o;
+    o.x = pack_bf16x2(v.x * r * bf16lo(g.x), v.y * r * bf16hi(g.x));
+    o.y = pack_bf16x2(v.z * r * bf16lo(g.y), v.w * r * bf16hi(g.y));
+    *reinterpret_cast<uint2*>(out + (size_t)t * H + k) = o;
+  }
+}
+
+// grid (T, heads); thread i < d/2 rotates the pair (i, i + d/2) of one head
+__global__ void rope_append_kernel(const float* __restrict__ qkv, int T, int p0, int slot,
+                                   const float* __restrict__ rope_cos, const float* __restrict__ rope_sin,
+                                   const int* __restrict__ block_table, int bt_stride, uint16_t* __restrict__ kpool,
+                                   uint16_t* __restrict__ vpool, int page_size, int q_heads, int kv_heads, int d,
+                                   uint16_t* __restrict__ q_out) {
+  const int t = blockIdx.x, h = blockIdx.y, i = threadIdx.x;
+  const int hd2 = d >> 1;
+  if (i >= hd2) return;
+  const int pos = p0 + t;
+  const int rows = (q_heads + 2 * kv_heads) * d;
+  const float* src = qkv + (size_t)t * rows + (size_t)h * d;
+  float v0 = src[i], v1 = src[i + hd2];
+  if (h < q_heads + kv_heads) {
+    const float c = rope_cos[(size_t)pos * hd2 + i], s = rope_sin[(size_t)pos * hd2 + i];
+    const float o0 = v0 * c - v1 * s, o1 = v1 * c + v0 * s;
+    v0 = o0;
+    v1 = o1;
+  }
+  if (h < q_heads) {
+    uint16_t* qp = q_out + (size_t)t * q_heads * d + (size_t)h * d + i;
+    qp[0] = f32_to_bf16_bits(v0);
+    qp[hd2] = f32_to_bf16_bits(v1);
+  } else {
+    const bool isk = h < q_heads + kv_heads;
+    const int kvh = isk ? h - q_heads : h - q_heads - kv_heads;
+    const int page = block_table[(size_t)slot * bt_stride + pos / page_size];
+    const int off = pos % page_size;
+    uint16_t* dst = (isk ? kpool : vpool) + (((size_t)page * kv_heads + kvh) * page_size + off) * d + i;
+    dst[0] = f32_to_bf16_bits(v0);
+    dst[hd2] = f32_to_bf16_bits(v1);
+  }
+}
+
+constexpr int PROWS = 8;  // query rows (= warps) per block
+
+template <int D, int G>
+__global__ void __launch_bounds__(PROWS * 32) prefill_attention_kernel(
+    const uint16_t* __restrict__ q, int T, int p0, int slot, const int* __restrict__ block_table, int bt_stride,
+    const uint16_t* __restrict__ kpool, const uint16_t* __restrict__ vpool, int page_size, int q_heads, int kv_heads,
+    uint16_t* __restrict__ out) {
+  constexpr int KSTRIDE = D + 8;
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  uint16_t* ks = reinterpret_cast<uint16_t*>(smem_raw);
+  uint16_t* vs = ks + ATT_TP * KSTRIDE;
+  float* qs = reinterpret_cast<float*>(vs + ATT_TP * KSTRIDE);  // [PROWS][G][D]
+
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int kvh = blockIdx.y;
+  const int t = blockIdx.x * PROWS + warp;
+  const bool live = t < T;
+  const int QD = q_heads * D;
+  const float scale = rsqrtf((float)D);
+
+  float* myq = qs + (size_t)warp * G * D;
+  if (live) {
+    const uint16_t* qr = q + (size_t)t * QD + (size_t)kvh * G * D;
+    for (int i = lane; i < G * D; i += 32) myq[i] = __uint_as_float((uint32_t)qr[i] << 16);
+  }
+  float m[G], l[G], o[G][D / 32];
+#pragma unroll
+  for (int j = 0; j < G; ++j) {
+    m[j] = -INFINITY;
+    l[j] = 0.f;
+#pragma unroll
+    for (int i = 0; i < D / 32; ++i) o[j][i] = 0.f;
+  }
+  const int tmax = min(T - 1, blockIdx.x * PROWS + PROWS - 1);
+  const int ntiles = (p0 + tmax + 1 + ATT_TP - 1) / ATT_TP;
+  const int myctx = live ? p0 + t + 1 : 0;
+
+  for (int tile = 0; tile < ntiles; ++tile) {
+    const int pbase = tile * ATT_TP;
+    const int tile_valid = min(ATT_TP, p0 + tmax + 1 - pbase);
+    const int page = block_table[(size_t)slot * bt_stride + pbase / page_size];
+    const size_t base = (((size_t)page * kv_heads + kvh) * page_size + (pbase % page_size)) * D;
+    __syncthreads();
+    for (int c = tid; c < ATT_TP * (D / 8); c += PROWS * 32) {
+      const int r = c / (D / 8), cc = c % (D / 8);
+      uint4 kk = make_uint4(0, 0, 0, 0), vv = kk;
+      if (r < tile_valid) {
+        kk = *reinterpret_cast<const uint4*>(kpool + base + (size_t)r * D + cc * 8);
+        vv = *reinterpret_cast<const uint4*>(vpool + base + (size_t)r * D + cc * 8);
+      }
+      *reinterpret_cast<uint4*>(ks + r * KSTRIDE + cc * 8) = kk;
+      *reinterpret_cast<uint4*>(vs + r * KSTRIDE + cc * 8) = vv;
+    }
+    __syncthreads();
+    const int valid = min(ATT_TP, myctx - pbase);
+    if (valid > 0) {
+#pragma unroll
+      for (int j = 0; j < G; ++j) attend_tile<D>(myq + j * D, ks, vs, KSTRIDE, valid, scale, m[j], l[j], o[j]);
+    }
+  }
+  if (live) {
+#pragma unroll
+    for (int j = 0; j < G; ++j) {
+      const float inv = 1.0f / l[j];
+      uint16_t* op = out + (size_t)t * QD + (size_t)(kvh * G + j) * D + lane * (D / 32);
+#pragma unroll
+      for (int i = 0; i < D / 32; ++i) op[i] = f32_to_bf16_bits(o[j][i] * inv);
+    }
+  }
+}
+
+template <int D, int G>
+cudaError_t launch_pa(const uint16_t* q, int T, int p0, int slot, const int* bt, int bt_stride, const uint16_t* kpool,
+                      const uint16_t* vpool, int page_size, int q_heads, int kv_heads, uint16_t* out,
+                      cudaStream_t s) {
+  const size_t smem = (size_t)2 * ATT_TP * (D + 8) * 2 + (size_t)PROWS * G * D * 4;
+  auto kern = prefill_attention_kernel<D, G>;
+  if (smem > 48 * 1024) {
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+  }
+  dim3 grid((T + PROWS - 1) / PROWS, kv_heads);
+  kern<<<grid, PROWS * 32, smem, s>>>(q, T, p0, slot, bt, bt_stride, kpool, vpool, page_size, q_heads, kv_heads, out);
+  return cudaGetLastError();
+}
+
+template <int D>
+cudaError_t launch_pa_g(int G, const uint16_t* q, int T, int p0, int slot, const int* bt, int bt_stride,
+                        const uint16_t* kpool, const uint16_t* vpool, int page_size, int q_heads, int kv_heads,
+                        uint16_t* out, cudaStream_t s) {
+  switch (G) {
+    case 1: return launch_pa<D, 1>(q, T, p0, slot, bt, bt_stride, kpool, vpool, page_size, q_heads, kv_heads, out, s);
+    case 2: return launch_pa<D, 2>(q, T, p0, slot, bt, bt_stride, kpool, vpool, page_size, q_heads, kv_heads, out, s);
+    case 4: return launch_pa<D, 4>(q, T, p0, slot, bt, bt_stride, kpool, vpool, page_size, q_heads, kv_heads, out, s);
+    case 8: return launch_pa<D, 8>(q, T, p0, slot, bt, bt_stride, kpool, vpool, page_size, q_heads, kv_heads, out, s);
+  }
+  return cudaErrorInvalidValue;
+}
+
+}  // namespace
+
+cudaError_t launch_embed_rows(const uint16_t* emb, const int* tokens, int T, int H, float* x, cudaStream_t s) {
+  embed_rows_kernel<<<T, 256, 0, s>>>(emb, tokens, T, H, x);
+  return cudaGetLastError();
+}
+
+cudaError_t launch_rmsnorm_rows(const float* x, const uint16_t* gain, float eps, int T, int H, uint16_t* out,
+                                cudaStream_t s) {
+  rmsnorm_rows_kernel<<<T, 256, 0, s>>>(x, gain, eps, T, H, out);
+  return cudaGetLastError();
+}
+
+cudaError_t launch_rope_append(const float* qkv, int T, int p0, int slot, const float* rope_cos,
+                               const float* rope_sin, const int* block_table, int bt_stride, uint16_t* kpool,
+                               uint16_t* vpool, int page_size, int q_heads, int kv_heads, int head_dim,
+                               uint16_t* q_out, cudaStream_t s) {
+  dim3 grid(T, q_heads + 2 * kv_heads);
+  rope_append_kernel<<<grid, head_dim / 2 < 32 ? 32 : head_dim / 2, 0, s>>>(
+      qkv, T, p0, slot, rope_cos, rope_sin, block_table, bt_stride, kpool, vpool, page_size, q_heads, kv_heads,
+      head_dim, q_out);
+  return cudaGetLastError();
+}
+
+cudaError_t launch_prefill_attention(const uint16_t* q, int T, int p0, int slot, const int* block_table,
+                                     int bt_stride, const uint16_t* kpool, const uint16_t* vpool, int page_size,
+                                     int q_heads, int kv_heads, int head_dim, uint16_t* out, cudaStream_t s) {
+  if (q_heads % kv_heads != 0 || page_size % ATT_TP != 0) return cudaErrorInvalidValue;
+  const int G = q_heads / kv_heads;
+  switch (head_dim) {
+    case 32: return launch_pa_g<32>(G, q, T, p0, slot, block_table, bt_stride, kpool, vpool, page_size, q_heads, kv_heads, out, s);
+    case 64: return launch_pa_g<64>(G, q, T, p0, slot, block_table, bt_stride, kpool, vpool, page_size, q_heads, kv_heads, out, s);
+    case 128: return launch_pa_g<128>(G, q, T, p0, slot, block_table, bt_stride, kpool, vpool, page_size, q_heads, kv_heads, out, s);
+  }
+  return cudaErrorInvalidValue;
+}
+
+}  // namespace llmc

@@ -1,0 +1,250 @@
+"""End-to-end parity of the engine (prefill + greedy decode through the C ABI of include/llmc.h)
+against the fp32 CPU oracle, on the same seeded random-init weights and the same token ids.
+
+Tolerance (BASELINE.json north_star): logits max-abs <= 2e-2 against the fp32 oracle, teacher-forced on
+the oracle's greedy tokens, and argmax agreement on the first 64 greedy tokens.  A free-running
+disagreement is accepted ONLY where the oracle's own top-2 margin at that step is inside the logit
+tolerance (a numerical tie that no bf16-activation implementation can be asked to resolve); the test
+reports when that clause was needed."""
+import json
+import os
+import subprocess
+import sys
+
+import numpy as np
+import pytest
+
+from oracle import ref
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+# bring-up switch: LLMC_TEST_PREFILL_IMPL=1 runs every engine test on the plain CUDA-core GEMM
+DEFAULT_IMPL = int(os.environ.get("LLMC_TEST_PREFILL_IMPL", "0"))
+
+
+@pytest.fixture(scope="session")
+def tc_ok(gpu):
+    """The tcgen05 GEMM passes a small self-check in a subprocess (a hang there must not hang pytest)."""
+    cmd = [sys.executable, os.path.join(ROOT, "tests", "_gemm_tc_check.py"), "130", "384", "256", "1", "0"]
+    try:
+        r = subprocess.run(cmd, capture_output=True, text=True, timeout=120)
+    except subprocess.TimeoutExpired:
+        return False
+    if r.returncode != 0:
+        return False
+    return json.loads(r.stdout.strip().splitlines()[-1])["bad_rows"] == 0
+
+
+@pytest.fixture(autouse=True)
+def _guard_tensor_core_path(request, gpu):
+    if DEFAULT_IMPL == 0 and not request.getfixturevalue("tc_ok"):
+        pytest.fail("tcgen05 GEMM self-check failed or hung; engine tests on the product prefill path not run "
+                    "(set LLMC_TEST_PREFILL_IMPL=1 to test the rest on the comparator GEMM)")
+
+pytestmark = pytest.mark.gpu
+TOL = 2e-2
+
+DIMS = {k: v for k, v in ref.SHAPES.items() if k not in ("llama-1b", "llama-8b")}
+
+
+def make_pair(llmc, name, seed, max_ctx=512, **kw):
+    o = ref.Oracle(name, seed=seed, max_ctx=max_ctx)
+    kw.setdefault("prefill_impl", DEFAULT_IMPL)
+    e = llmc.Engine(dims=DIMS[name], seed=seed, max_ctx=max_ctx, max_slots=kw.pop("max_slots", 4), **kw)
+    return o, e
+
+
+@pytest.mark.parametrize("name", ["tiny", "tiny-untied", "small-d128"])
+def test_weights_are_bit_identical_to_the_oracle(gpu, name):
+    o, e = make_pair(gpu, name, seed=21)
+    s = DIMS[name]
+    for layer in [-1] + list(range(s["layers"])):
+        kinds = [0, 1, 2] if layer < 0 else list(range(9))
+        for kind in kinds:
+            assert np.array_equal(e.debug_tensor(layer, kind), o.tensor(layer, kind)), (layer, kind)
+    e.close()
+
+
+@pytest.mark.parametrize("impl", [1, 0])
+@pytest.mark.parametrize("name,n_prompt", [("tiny", 1), ("tiny", 37), ("tiny-untied", 70), ("small-d128", 45)])
+def test_prefill_logits_and_kv(gpu, name, n_prompt, impl, request):
+    if impl == 0 and not request.getfixturevalue("tc_ok"):
+        pytest.fail("tcgen05 GEMM self-check failed or hung")
+    o, e = make_pair(gpu, name, seed=3, prefill_impl=impl)
+    V = DIMS[name]["vocab"]
+    toks = np.random.default_rng(n_prompt).integers(0, V, n_prompt)
+    want = o.forward(toks, "last")
+    slot = e.seq_alloc()
+    nxt, lg = e.prefill(slot, toks, want_logits=True)
+    err = np.abs(lg - want).max()
+    assert err <= TOL, "prefill logits max-abs %.3e (std %.3f)" % (err, want.std())
+    assert nxt == int(np.argmax(lg))
+    assert e.seq_len(slot) == n_prompt
+    e.seq_free(slot)
+    e.close()
+
+
+@pytest.mark.parametrize("flags", [0, 3, 1, 2])
+@pytest.mark.parametrize("name", ["tiny", "tiny-untied", "small-d128"])
+def test_teacher_forced_decode_logits(gpu, name, flags):
+    """Every decode step's logits against the oracle, both fed the ORACLE's greedy tokens."""
+    o, e = make_pair(gpu, name, seed=8, flags=flags)
+    V = DIMS[name]["vocab"]
+    prompt = np.random.default_rng(5).integers(0, V, 19)
+    n_new = 40
+    otoks, olog = o.generate(prompt, n_new, want_logits=True)
+    slot = e.seq_alloc()
+    nxt, lg = e.prefill(slot, prompt, want_logits=True)
+    worst = np.abs(lg - olog[0]).max()
+    agree = int(nxt == otoks[0])
+    for s in range(1, n_new):
+        e.set_next_token(slot, otoks[s - 1])
+        out, lg = e.decode([slot], 1, want_logits=True)
+        worst = max(worst, np.abs(lg[0] - olog[s]).max())
+        assert out[0, 0] == int(np.argmax(lg[0]))
+        agree += int(out[0, 0] == otoks[s])
+    assert worst <= TOL, "decode logits max-abs %.3e" % worst
+    assert e.seq_len(slot) == len(prompt) + n_new - 1
+    print("teacher-forced argmax agreement %d/%d, worst logit err %.2e" % (agree, n_new, worst))
+    e.close()
+
+
+def greedy_agreement(otoks, olog, gtoks, tol=TOL):
+    """Index of the first free-running disagreement that is NOT a numerical tie in the oracle, or -1."""
+    for s, (a, b) in enumerate(zip(otoks, gtoks)):
+        if a != b:
+            margin = float(olog[s][a] - olog[s][b])
+            return (s, margin) if margin > tol else (-2, margin)      # -2: diverged at a tie; stop comparing
+    return (-1, 0.0)
+
+
+@pytest.mark.parametrize("name", ["tiny", "tiny-untied", "small-d128"])
+@pytest.mark.parametrize("chunk", [1, 7, 64])
+def test_free_running_greedy_tokens(gpu, name, chunk):
+    o, e = make_pair(gpu, name, seed=13)
+    V = DIMS[name]["vocab"]
+    prompt = np.random.default_rng(9).integers(0, V, 33)
+    n_new = 64
+    otoks, olog = o.generate(prompt, n_new, want_logits=True)
+    gtoks = e.generate(prompt, n_new, chunk=chunk)
+    where, margin = greedy_agreement(otoks, olog, gtoks)
+    assert where < 0, "greedy tokens diverge at step %d with oracle margin %.3e > tol" % (where, margin)
+    if where == -2:
+        print("NOTE: free-running divergence at an oracle near-tie (margin %.2e <= %.0e)" % (margin, TOL))
+    e.close()
+
+
+def test_chunked_prefill_equals_single_pass(gpu):
+    o, e = make_pair(gpu, "tiny", seed=2, prefill_chunk=32)
+    _, e2 = make_pair(gpu, "tiny", seed=2, prefill_chunk=2048)
+    toks = np.random.default_rng(1).integers(0, 1024, 150)
+    s1, s2 = e.seq_alloc(), e2.seq_alloc()
+    n1, l1 = e.prefill(s1, toks, want_logits=True)        # 5 chunks of 32 (ragged last)
+    n2, l2 = e2.prefill(s2, toks, want_logits=True)
+    want = o.forward(toks, "last")
+    assert np.abs(l1 - want).max() <= TOL and np.abs(l2 - want).max() <= TOL
+    assert np.abs(l1 - l2).max() <= 5e-3
+    # split prompt over two llmc_prefill calls (prefix reuse)
+    s3 = e.seq_alloc()
+    e.prefill(s3, toks[:70])
+    n3, l3 = e.prefill(s3, toks[70:], want_logits=True)
+    assert np.abs(l3 - want).max() <= TOL and e.seq_len(s3) == 150
+    e.close(); e2.close()
+
+
+@pytest.mark.parametrize("B", [2, 3, 5, 8])
+def test_batched_decode_matches_per_sequence_oracle(gpu, B):
+    name = "tiny"
+    V = DIMS[name]["vocab"]
+    e = gpu.Engine(dims=DIMS[name], seed=4, max_ctx=256, max_slots=8, prefill_impl=DEFAULT_IMPL)
+    rng = np.random.default_rng(B)
+    prompts = [rng.integers(0, V, int(n)) for n in rng.integers(3, 90, B)]
+    slots, firsts = [], []
+    for p in prompts:
+        s = e.seq_alloc()
+        slots.append(s)
+        firsts.append(e.prefill(s, p))
+    n_new = 12
+    out, lg = e.decode(slots, n_new, want_logits=True)
+    for i, p in enumerate(prompts):
+        o = ref.Oracle(name, seed=4, max_ctx=256)
+        otoks, olog = o.generate(p, n_new + 1, want_logits=True)
+        gt = [firsts[i]] + out[i].tolist()
+        where, margin = greedy_agreement(otoks, olog, gt)
+        assert where < 0, (i, where, margin)
+        if where == -1:
+            assert np.abs(lg[i] - olog[n_new]).max() <= TOL
+    e.close()
+
+
+def test_slots_are_independent_and_reusable(gpu):
+    e = gpu.Engine(dims=DIMS["tiny"], seed=6, max_ctx=128, max_slots=2, prefill_impl=DEFAULT_IMPL)
+    p = np.arange(1, 30)
+    a = e.generate(p, 10)
+    s0 = e.seq_alloc(); s1 = e.seq_alloc()
+    with pytest.raises(gpu.LlmcError) as ei:
+        e.seq_alloc()
+    assert ei.value.code == gpu.ERR_LIMIT
+    e.prefill(s0, [5, 6, 7])
+    e.seq_free(s0); e.seq_free(s1)
+    b = e.generate(p, 10)                                  # same pages, recycled
+    assert a.tolist() == b.tolist()
+    e.close()
+
+
+def test_error_paths(gpu):
+    e = gpu.Engine(dims=DIMS["tiny"], seed=6, max_ctx=64, max_slots=2, prefill_impl=DEFAULT_IMPL)
+    s = e.seq_alloc()
+    with pytest.raises(gpu.LlmcError) as ei:
+        e.decode([s], 1)                                   # nothing prefilled
+    assert ei.value.code == gpu.ERR_STATE
+    with pytest.raises(gpu.LlmcError) as ei:
+        e.prefill(s, [5000])                               # token out of range
+    assert ei.value.code == gpu.ERR_INVALID
+    with pytest.raises(gpu.LlmcError) as ei:
+        e.prefill(s, list(range(65)))                      # beyond max_ctx
+    assert ei.value.code == gpu.ERR_LIMIT
+    e.prefill(s, list(range(60)))
+    with pytest.raises(gpu.LlmcError) as ei:
+        e.decode([s], 10)                                  # would overflow the context
+    assert ei.value.code == gpu.ERR_LIMIT
+    with pytest.raises(gpu.LlmcError) as ei:
+        e.decode([s, s], 1)
+    assert ei.value.code == gpu.ERR_INVALID
+    with pytest.raises(gpu.LlmcError) as ei:
+        e.seq_free(1)
+    assert ei.value.code == gpu.ERR_STATE
+    assert e.decode([s], 4).shape == (1, 4)                # still usable after the errors
+    e.close()
+
+
+def test_config2_llama1b_512_prompt_256_decode(gpu):
+    """BASELINE.json configs[1] at full size: Llama-3.2-1B shape, seed 0, 512-token prompt, 256 greedy
+    tokens; logits teacher-forced on the oracle's tokens, every step, max-abs <= 2e-2; argmax
+    agreement on the first 64 free-running tokens (numerical ties in the oracle excepted)."""
+    n_prompt, n_new = 512, 256
+    o = ref.Oracle("llama-1b", seed=0, max_ctx=1024)
+    prompt = np.random.default_rng(1).integers(0, 128256, n_prompt)
+    otoks, olog = o.generate(prompt, n_new, want_logits=True)
+    e = gpu.Engine(shape=gpu.SHAPE_LLAMA_1B, seed=0, max_ctx=1024, max_slots=2, prefill_impl=DEFAULT_IMPL)
+    # free-running
+    gtoks = e.generate(prompt, n_new)
+    where, margin = greedy_agreement(otoks[:64], olog[:64], gtoks[:64])
+    n_same = int((np.asarray(gtoks) == otoks).sum())
+    print("free-running: %d/%d tokens equal; first-64 check -> %s (margin %.3e)" % (n_same, n_new, where, margin))
+    assert where < 0, "first 64 greedy tokens diverge at %d with oracle margin %.3e" % (where, margin)
+    # teacher-forced logits
+    slot = e.seq_alloc()
+    nxt, lg = e.prefill(slot, prompt, want_logits=True)
+    errs = [float(np.abs(lg - olog[0]).max())]
+    agree = int(nxt == otoks[0])
+    for s in range(1, n_new):
+        e.set_next_token(slot, otoks[s - 1])
+        out, lg = e.decode([slot], 1, want_logits=True)
+        errs.append(float(np.abs(lg[0] - olog[s]).max()))
+        agree += int(out[0, 0] == otoks[s])
+    print("teacher-forced: worst logit err %.3e (prefill %.3e), argmax agreement %d/%d, logit std %.3f"
+          % (max(errs), errs[0], agree, n_new, float(olog.std())))
+    assert max(errs) <= TOL
+    st = e.stats()
+    assert st["kernel_launches"] > 0
+    e.close()
