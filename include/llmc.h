@@ -69,13 +69,15 @@ typedef struct llmc_config {
 
 #define LLMC_FLAG_NO_GRAPH 1 /* launch decode kernels one by one instead of as a CUDA graph */
 #define LLMC_FLAG_NO_PDL 2   /* no programmatic dependent launch between decode kernels */
+#define LLMC_FLAG_KV_BF16 4  /* store the KV cache in bf16 (default fp32; see DESIGN.md "precision") */
+#define LLMC_FLAG_PREFILL_BF16 8 /* prefill GEMM activations as one bf16 (default: a bf16 hi+lo pair) */
 
 typedef struct llmc_stats {
   uint64_t kernel_launches;  /* kernels of this library launched since create (graph nodes counted) */
   uint64_t decode_steps;
   uint64_t prefill_tokens;
   double weight_bytes;       /* bf16 bytes streamed per decode step: layers + LM head + gains */
-  double kv_bytes_per_token; /* 2 * kv_heads * head_dim * 2 B * layers */
+  double kv_bytes_per_token; /* 2 * kv_heads * head_dim * layers * (4 B fp32 | 2 B bf16) */
   float last_prefill_ms;     /* CUDA-event time of the last llmc_prefill on the engine's stream */
   float last_decode_ms;      /* CUDA-event time of the last llmc_decode (all its steps) */
   int32_t graph_enabled, pdl_enabled;

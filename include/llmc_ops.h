@@ -36,36 +36,40 @@ int llmc_op_lmhead(int device, int V, int K, int B, const uint16_t* W, const flo
                    float eps, float* logits, int32_t* tok);
 
 /* Single-query attention over a paged cache built from dense K/V:
- *   q [B][q_heads*d] fp32; k, v [B][max_ctx][kv_heads*d] bf16; ctx[b] tokens valid; out like q.
- * nsplit = 0 picks the engine's default.  Pages are assigned in a scrambled order. */
+ *   q [B][q_heads*d] fp32; k, v [B][max_ctx][kv_heads*d] bf16 bits (kv_fp32 = 0) or fp32 (1);
+ *   ctx[b] tokens valid; out like q.  nsplit = 0 picks the engine's default.  Pages are assigned
+ *   in a scrambled order and unwritten slots hold NaN patterns. */
 int llmc_op_attn_decode(int device, int B, int q_heads, int kv_heads, int head_dim, int page_size, int nsplit,
-                        int max_ctx, const int32_t* ctx, const float* q, const uint16_t* k, const uint16_t* v,
+                        int max_ctx, int kv_fp32, const int32_t* ctx, const float* q, const void* k, const void* v,
                         float* out);
 
-/* Prefill GEMM C = A W^T.  impl 0: tcgen05; 1: plain CUDA-core comparator.  epi: 0 bf16 store,
- * 1 f32 store, 2 f32 residual add (out is in/out), 3 SwiGLU on logical Wg|Wu given as
- * W = [Wg ; Wu] ([2I][K], packed inside), out bf16 [T][I]. */
-int llmc_op_gemm(int device, int impl, int epi, int T, int N, int K, const uint16_t* A, const uint16_t* W,
-                 void* out);
+/* Prefill GEMM C = (A + A_lo) W^T.  A_lo may be NULL (single bf16 operand).  impl 0: tcgen05;
+ * 1: plain CUDA-core comparator.  epi: 0 bf16 store, 1 f32 store, 2 f32 residual add (out is
+ * in/out), 3 SwiGLU on logical Wg|Wu given as W = [Wg ; Wu] ([2I][K], packed inside), out bf16
+ * [T][I] with the optional low half in out_lo (NULL otherwise). */
+int llmc_op_gemm(int device, int impl, int epi, int T, int N, int K, const uint16_t* A, const uint16_t* A_lo,
+                 const uint16_t* W, void* out, void* out_lo);
 
-/* Row-wise RMSNorm fp32 -> bf16. */
-int llmc_op_rmsnorm_rows(int device, int T, int H, const float* x, const uint16_t* gain, float eps, uint16_t* out);
+/* Row-wise RMSNorm fp32 -> bf16 (hi, and lo if out_lo != NULL: x = hi + lo). */
+int llmc_op_rmsnorm_rows(int device, int T, int H, const float* x, const uint16_t* gain, float eps, uint16_t* out,
+                         uint16_t* out_lo);
 
 /* RoPE + KV append + causal attention of T new rows at positions p0..p0+T-1:
- *   qkv [T][(nq+2nkv)*d] fp32 (pre-RoPE) for the new rows; k_past, v_past [p0][nkv*d] bf16
- *   (already rotated) for the cached prefix; out bf16 [T][nq*d]; q_out bf16 [T][nq*d];
- *   k_new, v_new bf16 [T][nkv*d] read back from the pages. */
+ *   qkv [T][(nq+2nkv)*d] fp32 (pre-RoPE) for the new rows; k_past, v_past [p0][nkv*d] (already
+ *   rotated) for the cached prefix, bf16 bits or fp32 per kv_fp32; out (+ out_lo, may be NULL)
+ *   bf16 [T][nq*d]; q_out fp32 [T][nq*d]; k_new, v_new [T][nkv*d] read back from the pages. */
 int llmc_op_prefill_attention(int device, int T, int p0, int q_heads, int kv_heads, int head_dim, int page_size,
-                              float rope_theta, const float* qkv, const uint16_t* k_past, const uint16_t* v_past,
-                              uint16_t* out, uint16_t* q_out, uint16_t* k_new, uint16_t* v_new);
+                              float rope_theta, int kv_fp32, const float* qkv, const void* k_past, const void* v_past,
+                              uint16_t* out, uint16_t* out_lo, float* q_out, void* k_new, void* v_new);
 
 /* Read a LOGICAL weight tensor of an engine back (un-packing the HBM layout); kinds as in the
  * oracle: layer -1: 0 embedding, 1 lm head, 2 final gain; layer >= 0: 0 g1, 1 wq, 2 wk, 3 wv,
  * 4 wo, 5 g2, 6 wg, 7 wu, 8 wd.  Returns the element count (or < 0); copies if cap suffices. */
 int64_t llmc_debug_tensor(llmc_engine* e, int layer, int kind, uint16_t* out, int64_t cap);
 
-/* Read the cached K and V rows ([kv_heads*d] bf16 each) of one position of a slot. */
-int llmc_debug_kv(llmc_engine* e, int slot, int layer, int pos, uint16_t* k, uint16_t* v);
+/* Read the cached K and V rows ([kv_heads*d] each, in the engine's KV element type) of one
+ * position of a slot. */
+int llmc_debug_kv(llmc_engine* e, int slot, int layer, int pos, void* k, void* v);
 
 #ifdef __cplusplus
 }

@@ -12,10 +12,10 @@
 //               per layer: g1[H] | Wqkv[(nq+2nkv)d][H] | Wo[H][nq d] | g2[H] |
 //                          Wgu[2I][H] (gate/up interleaved in blocks of 64 rows) | Wd[H][I]
 //               global:    E[V][H] | LMHead[V][H] (= E when tied) | gf[H]
-//   KV pool   K and V: [layer][page][kv_head][page_size][d] bf16; block table [slot][page]
+//   KV pool   K and V: [layer][page][kv_head][page_size][d], fp32 (default) or bf16; block table [slot][page]
 //   decode    x[B][H], q[B][nq d], attn[B][nq d], act[B][I] fp32; split-attention scratch
-//   prefill   x[T][H] fp32, xn[T][H] bf16, qkv[T][(nq+2nkv)d] fp32, q/attn[T][nq d] bf16,
-//             act[T][I] bf16 for T = prefill_chunk
+//   prefill   x[T][H] fp32, qkv[T][(nq+2nkv)d] fp32, q[T][nq d] fp32; GEMM operands xn[T][H],
+//             attn[T][nq d], act[T][I] as bf16 hi (+ lo) pairs, for T = prefill_chunk
 #include <cuda_runtime.h>
 #include <math.h>
 #include <string.h>
@@ -135,7 +135,7 @@ int init_weights(llmc_engine* e) {
   E_TRY(launch_init_gain(e->gf, H, e->seed, tensor_id(-1, K_FINAL_NORM), s));
   e->stats.kernel_launches += (uint64_t)d.layers * 9 + 3;
   e->stats.weight_bytes = 2.0 * ((double)per_layer * d.layers + (double)V * H + H);
-  e->stats.kv_bytes_per_token = 2.0 * 2.0 * KD * d.layers;
+  e->stats.kv_bytes_per_token = 2.0 * e->kv_elem * KD * d.layers;
   return LLMC_OK;
 }
 
@@ -157,9 +157,10 @@ int ensure_pages(llmc_engine* e, int slot, int need_tokens) {
   return LLMC_OK;
 }
 
-int gemm(llmc_engine* e, const uint16_t* A, const uint16_t* W, void* out, int T, int N, int K, int epi) {
-  if (e->prefill_impl == 0) E_TRY(launch_gemm_tcgen05(A, W, out, T, N, K, epi, e->stream));
-  else E_TRY(launch_gemm_simple(A, W, out, T, N, K, epi, e->stream));
+int gemm(llmc_engine* e, const uint16_t* A, const uint16_t* Alo, const uint16_t* W, void* out, void* out_lo, int T,
+         int N, int K, int epi) {
+  if (e->prefill_impl == 0) E_TRY(launch_gemm_tcgen05(A, Alo, W, out, out_lo, T, N, K, epi, e->stream));
+  else E_TRY(launch_gemm_simple(A, Alo, W, out, out_lo, T, N, K, epi, e->stream));
   e->stats.kernel_launches++;
   return LLMC_OK;
 }
@@ -178,6 +179,7 @@ GemvArgs base_args(llmc_engine* e, int B) {
   a.block_table = e->d_block_table;
   a.bt_stride = e->pages_per_seq;
   a.page_size = e->page_size;
+  a.kv_fp32 = e->kv_fp32;
   a.q_heads = d.q_heads;
   a.kv_heads = d.kv_heads;
   a.head_dim = d.head_dim;
@@ -204,15 +206,14 @@ int lm_head(llmc_engine* e, const float* xin, int64_t x_stride, int B, const int
 }
 
 // enqueue one decode step for the B sequences listed in d_slots
-int enqueue_decode_step(llmc_engine* e, int B, bool want_logits) {
+int enqueue_decode_step(llmc_engine* e, int B, bool want_logits, int nsplit) {
   const ModelDims& d = e->d;
   const int H = d.hidden, QD = d.qd(), I = d.inter, bt = batch_tile(B);
   const bool pdl = e->use_pdl;
-  const int nsplit = attn_decode_default_nsplit(B, d.kv_heads);
   for (int l = 0; l < d.layers; ++l) {
     const LayerW& w = e->L[l];
-    uint16_t* kp = e->kpool + (size_t)l * e->kv_layer_stride;
-    uint16_t* vp = e->vpool + (size_t)l * e->kv_layer_stride;
+    unsigned char* kp = e->kpool + (size_t)l * e->kv_layer_stride * e->kv_elem;
+    unsigned char* vp = e->vpool + (size_t)l * e->kv_layer_stride * e->kv_elem;
     {  // RMSNorm -> QKV -> RoPE -> KV append   (layer 0 also gathers the embedding)
       GemvArgs a = base_args(e, B);
       a.W = w.wqkv; a.N = d.qkv_rows(); a.K = H;
@@ -225,7 +226,7 @@ int enqueue_decode_step(llmc_engine* e, int B, bool want_logits) {
     {
       AttnDecodeArgs a;
       memset(&a, 0, sizeof(a));
-      a.q = e->q; a.out = e->attn; a.kpool = kp; a.vpool = vp;
+      a.q = e->q; a.out = e->attn; a.kpool = kp; a.vpool = vp; a.kv_fp32 = e->kv_fp32;
       a.slots = e->d_slots; a.seq_len = e->d_seq_len; a.ctx_extra = 1;
       a.block_table = e->d_block_table; a.bt_stride = e->pages_per_seq;
       a.page_size = e->page_size; a.q_heads = d.q_heads; a.kv_heads = d.kv_heads; a.head_dim = d.head_dim;
@@ -259,8 +260,8 @@ int enqueue_decode_step(llmc_engine* e, int B, bool want_logits) {
                  pdl);
 }
 
-int get_graph(llmc_engine* e, int B, bool want_logits, cudaGraphExec_t* out) {
-  const int key = B * 2 + (want_logits ? 1 : 0);
+int get_graph(llmc_engine* e, int B, bool want_logits, int nsplit, cudaGraphExec_t* out) {
+  const int key = (B * 2 + (want_logits ? 1 : 0)) * 16 + nsplit;
   auto it = e->graphs.find(key);
   if (it != e->graphs.end()) {
     *out = it->second;
@@ -268,7 +269,7 @@ int get_graph(llmc_engine* e, int B, bool want_logits, cudaGraphExec_t* out) {
   }
   const uint64_t launches_before = e->stats.kernel_launches;
   E_TRY(cudaStreamBeginCapture(e->stream, cudaStreamCaptureModeRelaxed));
-  int rc = enqueue_decode_step(e, B, want_logits);
+  int rc = enqueue_decode_step(e, B, want_logits, nsplit);
   cudaGraph_t g = nullptr;
   cudaError_t ce = cudaStreamEndCapture(e->stream, &g);
   e->stats.kernel_launches = launches_before;  // capture launched nothing
@@ -331,6 +332,9 @@ static int create_impl(llmc_engine* e, const llmc_config& c) {
   e->prefill_chunk = c.prefill_chunk; e->prefill_impl = c.prefill_impl;
   e->use_graph = !(c.flags & LLMC_FLAG_NO_GRAPH);
   e->use_pdl = !(c.flags & LLMC_FLAG_NO_PDL);
+  e->kv_fp32 = (c.flags & LLMC_FLAG_KV_BF16) ? 0 : 1;
+  e->kv_elem = e->kv_fp32 ? 4 : 2;
+  e->split_prefill = !(c.flags & LLMC_FLAG_PREFILL_BF16);
   e->stats.sm_count = e->prop.multiProcessorCount; e->stats.cc_major = e->prop.major; e->stats.cc_minor = e->prop.minor;
   E_TRY(cudaStreamCreateWithFlags(&e->stream, cudaStreamNonBlocking));
   E_TRY(cudaEventCreate(&e->ev0));
@@ -344,8 +348,8 @@ static int create_impl(llmc_engine* e, const llmc_config& c) {
   e->pages_per_seq = (e->max_ctx + e->page_size - 1) / e->page_size;
   e->num_pages = e->pages_per_seq * e->max_slots;
   e->kv_layer_stride = (size_t)e->num_pages * KD * e->page_size;
-  if (int rc = dalloc(e, &e->kpool, e->kv_layer_stride * d.layers)) return rc;
-  if (int rc = dalloc(e, &e->vpool, e->kv_layer_stride * d.layers)) return rc;
+  if (int rc = dalloc(e, &e->kpool, e->kv_layer_stride * d.layers * e->kv_elem)) return rc;
+  if (int rc = dalloc(e, &e->vpool, e->kv_layer_stride * d.layers * e->kv_elem)) return rc;
   if (int rc = dalloc(e, &e->d_block_table, (size_t)e->max_slots * e->pages_per_seq)) return rc;
   E_TRY(cudaMemsetAsync(e->d_block_table, 0, (size_t)e->max_slots * e->pages_per_seq * sizeof(int), e->stream));
   e->h_block_table.assign((size_t)e->max_slots * e->pages_per_seq, 0);
@@ -385,12 +389,7 @@ static int create_impl(llmc_engine* e, const llmc_config& c) {
   if (int rc = dalloc(e, &e->part_idx, (size_t)MB * lmb)) return rc;
   if (int rc = dalloc(e, &e->lm_counter, 1)) return rc;
   if (int rc = dalloc(e, &e->attn_counters, (size_t)MB * d.kv_heads)) return rc;
-  size_t sc = 0;
-  for (int B = 1; B <= MB; ++B) {
-    size_t n = attn_decode_scratch_floats(B, d.q_heads, attn_decode_default_nsplit(B, d.kv_heads), D);
-    if (n > sc) sc = n;
-  }
-  if (int rc = dalloc(e, &e->attn_scratch, sc)) return rc;
+  if (int rc = dalloc(e, &e->attn_scratch, attn_decode_scratch_floats(MB, d.q_heads, ATTN_MAX_SPLIT, D))) return rc;
   if (int rc = dalloc(e, &e->d_out_tokens, (size_t)MB * MAX_STEPS_PER_CALL)) return rc;
   if (int rc = dalloc(e, &e->d_step_counter, 1)) return rc;
   if (int rc = dalloc(e, &e->d_dummy_counter, 1)) return rc;
@@ -407,6 +406,11 @@ static int create_impl(llmc_engine* e, const llmc_config& c) {
   if (int rc = dalloc(e, &e->pq, (size_t)TC * QD)) return rc;
   if (int rc = dalloc(e, &e->pattn, (size_t)TC * QD)) return rc;
   if (int rc = dalloc(e, &e->pact, (size_t)TC * I)) return rc;
+  if (e->split_prefill) {
+    if (int rc = dalloc(e, &e->pxn_lo, (size_t)TC * H)) return rc;
+    if (int rc = dalloc(e, &e->pattn_lo, (size_t)TC * QD)) return rc;
+    if (int rc = dalloc(e, &e->pact_lo, (size_t)TC * I)) return rc;
+  }
   E_TRY(cudaStreamSynchronize(e->stream));
   E_TRY(cudaGetLastError());
   e->stats.graph_enabled = e->use_graph;
@@ -530,18 +534,18 @@ int llmc_prefill(llmc_engine* e, int32_t slot, const int32_t* tokens, int32_t n,
     E_TRY(launch_embed_rows(e->emb, e->p_tokens, T, H, e->px, s));
     for (int l = 0; l < d.layers; ++l) {
       const LayerW& w = e->L[l];
-      uint16_t* kp = e->kpool + (size_t)l * e->kv_layer_stride;
-      uint16_t* vp = e->vpool + (size_t)l * e->kv_layer_stride;
-      E_TRY(launch_rmsnorm_rows(e->px, w.g1, d.rms_eps, T, H, e->pxn, s));
-      if (int rc = gemm(e, e->pxn, w.wqkv, e->pqkv, T, QD + 2 * KD, H, GEMM_STORE_F32)) return rc;
+      unsigned char* kp = e->kpool + (size_t)l * e->kv_layer_stride * e->kv_elem;
+      unsigned char* vp = e->vpool + (size_t)l * e->kv_layer_stride * e->kv_elem;
+      E_TRY(launch_rmsnorm_rows(e->px, w.g1, d.rms_eps, T, H, e->pxn, e->pxn_lo, s));
+      if (int rc = gemm(e, e->pxn, e->pxn_lo, w.wqkv, e->pqkv, nullptr, T, QD + 2 * KD, H, GEMM_STORE_F32)) return rc;
       E_TRY(launch_rope_append(e->pqkv, T, p0, slot, e->rope_cos, e->rope_sin, e->d_block_table, e->pages_per_seq,
-                               kp, vp, e->page_size, d.q_heads, d.kv_heads, d.head_dim, e->pq, s));
-      E_TRY(launch_prefill_attention(e->pq, T, p0, slot, e->d_block_table, e->pages_per_seq, kp, vp, e->page_size,
-                                     d.q_heads, d.kv_heads, d.head_dim, e->pattn, s));
-      if (int rc = gemm(e, e->pattn, w.wo, e->px, T, H, QD, GEMM_RESID_F32)) return rc;
-      E_TRY(launch_rmsnorm_rows(e->px, w.g2, d.rms_eps, T, H, e->pxn, s));
-      if (int rc = gemm(e, e->pxn, w.wgu, e->pact, T, 2 * I, H, GEMM_SWIGLU_BF16)) return rc;
-      if (int rc = gemm(e, e->pact, w.wd, e->px, T, H, I, GEMM_RESID_F32)) return rc;
+                               kp, vp, e->kv_fp32, e->page_size, d.q_heads, d.kv_heads, d.head_dim, e->pq, s));
+      E_TRY(launch_prefill_attention(e->pq, T, p0, slot, e->d_block_table, e->pages_per_seq, kp, vp, e->kv_fp32,
+                                     e->page_size, d.q_heads, d.kv_heads, d.head_dim, e->pattn, e->pattn_lo, s));
+      if (int rc = gemm(e, e->pattn, e->pattn_lo, w.wo, e->px, nullptr, T, H, QD, GEMM_RESID_F32)) return rc;
+      E_TRY(launch_rmsnorm_rows(e->px, w.g2, d.rms_eps, T, H, e->pxn, e->pxn_lo, s));
+      if (int rc = gemm(e, e->pxn, e->pxn_lo, w.wgu, e->pact, e->pact_lo, T, 2 * I, H, GEMM_SWIGLU_BF16)) return rc;
+      if (int rc = gemm(e, e->pact, e->pact_lo, w.wd, e->px, nullptr, T, H, I, GEMM_RESID_F32)) return rc;
     }
     e->stats.kernel_launches += 1 + (uint64_t)d.layers * 4;
   }
@@ -589,9 +593,14 @@ int llmc_decode(llmc_engine* e, const int32_t* slots, int32_t nslots, int32_t ns
   E_TRY(cudaMemcpyAsync(e->d_slots, slots, (size_t)nslots * sizeof(int), cudaMemcpyHostToDevice, s));
   E_TRY(cudaMemsetAsync(e->d_step_counter, 0, sizeof(int), s));
   const bool want_logits = logits != nullptr;
+  int max_len = 0;
+  for (int i = 0; i < nslots; ++i) max_len = std::max(max_len, e->h_seq_len[slots[i]]);
+  // blocks per (sequence, kv head) in the attention kernel, fixed for this call from the longest
+  // context it will reach (the graph is keyed by it)
+  const int nsplit = attn_decode_nsplit(max_len + nsteps);
   cudaGraphExec_t ge = nullptr;
   if (e->use_graph) {
-    int rc = get_graph(e, nslots, want_logits, &ge);
+    int rc = get_graph(e, nslots, want_logits, nsplit, &ge);
     if (rc != LLMC_OK) return rc;
   }
   E_TRY(cudaEventRecord(e->ev0, s));
@@ -600,7 +609,7 @@ int llmc_decode(llmc_engine* e, const int32_t* slots, int32_t nslots, int32_t ns
       E_TRY(cudaGraphLaunch(ge, s));
       e->stats.kernel_launches += (uint64_t)d.layers * 5 + 1;
     } else {
-      if (int rc = enqueue_decode_step(e, nslots, want_logits)) return rc;
+      if (int rc = enqueue_decode_step(e, nslots, want_logits, nsplit)) return rc;
     }
   }
   E_TRY(cudaEventRecord(e->ev1, s));

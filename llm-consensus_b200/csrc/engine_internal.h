@@ -32,8 +32,10 @@ struct llmc_engine {
   std::vector<llmc::LayerW> L;
   uint16_t *emb = nullptr, *lmhead = nullptr, *gf = nullptr;
   // kv
-  uint16_t *kpool = nullptr, *vpool = nullptr;
-  size_t kv_layer_stride = 0;
+  unsigned char *kpool = nullptr, *vpool = nullptr;  // bf16 or fp32 elements
+  size_t kv_layer_stride = 0;                        // elements per layer
+  int kv_fp32 = 1, kv_elem = 4;
+  bool split_prefill = true;
   int* d_block_table = nullptr;
   std::vector<int> h_block_table;
   std::vector<int> free_pages;
@@ -52,9 +54,10 @@ struct llmc_engine {
   int *d_out_tokens = nullptr, *d_step_counter = nullptr, *d_dummy_counter = nullptr, *d_pslot = nullptr;
   // prefill workspace
   int* p_tokens = nullptr;
-  float *px = nullptr, *pqkv = nullptr;
-  uint16_t *pxn = nullptr, *pq = nullptr, *pattn = nullptr, *pact = nullptr;
-  std::map<int, cudaGraphExec_t> graphs;  // key = B * 2 + want_logits
+  float *px = nullptr, *pqkv = nullptr, *pq = nullptr;
+  uint16_t *pxn = nullptr, *pattn = nullptr, *pact = nullptr;
+  uint16_t *pxn_lo = nullptr, *pattn_lo = nullptr, *pact_lo = nullptr;  // split-bf16 low halves (or NULL)
+  std::map<int, cudaGraphExec_t> graphs;  // key = (B * 2 + want_logits) * 16 + nsplit
   std::mutex mu;
   std::string last_error;
   llmc_stats stats{};

@@ -91,20 +91,24 @@ __host__ __device__ constexpr uint32_t make_idesc(int n) {
   return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(n >> 3) << 17) | ((uint32_t)(BM >> 4) << 24);
 }
 
-template <int BN>
+// SPLIT: A is given as a bf16 pair A_hi + A_lo (16 mantissa bits); each k-step then issues the
+// MMAs twice against the same W tile, accumulating A_hi W + A_lo W in TMEM.
+template <int BN, bool SPLIT>
 struct TileCfg {
-  static constexpr int STAGES = BN == 256 ? 4 : 6;
   static constexpr int A_BYTES = BM * BK * 2;
+  static constexpr int A_TILES = SPLIT ? 2 : 1;
   static constexpr int B_BYTES = BN * BK * 2;
-  static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
+  static constexpr int STAGE_BYTES = A_TILES * A_BYTES + B_BYTES;
+  static constexpr int STAGES = (200 * 1024 / STAGE_BYTES) > 6 ? 6 : (200 * 1024 / STAGE_BYTES);
   static constexpr int SMEM = STAGES * STAGE_BYTES + 1024 /*alignment slack*/ + 256 /*barriers*/;
 };
 
-template <int BN, int EPI>
+template <int BN, int EPI, bool SPLIT>
 __global__ void __launch_bounds__(GEMM_THREADS, 1)
-    gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmW,
-                   void* __restrict__ out, int T, int N, int K) {
-  using C = TileCfg<BN>;
+    gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmAlo,
+                   const __grid_constant__ CUtensorMap tmW, void* __restrict__ out, void* __restrict__ out_lo, int T,
+                   int N, int K) {
+  using C = TileCfg<BN, SPLIT>;
   extern __shared__ unsigned char smem_raw[];
   const uint32_t raw = smem_u32(smem_raw);
   const uint32_t base = (raw + 1023u) & ~1023u;  // SWIZZLE_128B operands need 1024-byte alignment
@@ -122,6 +126,7 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1)
   if (threadIdx.x == 0) {
     asm volatile("prefetch.tensormap [%0];" ::"l"(&tmA) : "memory");
     asm volatile("prefetch.tensormap [%0];" ::"l"(&tmW) : "memory");
+    if (SPLIT) asm volatile("prefetch.tensormap [%0];" ::"l"(&tmAlo) : "memory");
     for (int s = 0; s < C::STAGES; ++s) {
       mbar_init(full_bar(s), 1);
       mbar_init(empty_bar(s), 1);
@@ -149,7 +154,8 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1)
         mbar_expect_tx(full_bar(s), C::STAGE_BYTES);
         const uint32_t sa = base + s * C::STAGE_BYTES;
         tma_load_2d(sa, &tmA, kb * BK, m0, full_bar(s));
-        tma_load_2d(sa + C::A_BYTES, &tmW, kb * BK, n0, full_bar(s));
+        if (SPLIT) tma_load_2d(sa + C::A_BYTES, &tmAlo, kb * BK, m0, full_bar(s));
+        tma_load_2d(sa + C::A_TILES * C::A_BYTES, &tmW, kb * BK, n0, full_bar(s));
       }
     }
   } else if (warp == 1) {
@@ -161,12 +167,15 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1)
         mbar_wait(full_bar(s), ph);
         tc_fence_after();
         const uint32_t sa = base + s * C::STAGE_BYTES;
-        const uint32_t sb = sa + C::A_BYTES;
+        const uint32_t sb = sa + C::A_TILES * C::A_BYTES;
 #pragma unroll
-        for (int k = 0; k < BK / UMMA_K; ++k) {
-          const uint64_t da = make_smem_desc(sa + k * UMMA_K * 2);
-          const uint64_t db = make_smem_desc(sb + k * UMMA_K * 2);
-          tc_mma_bf16(tmem_base, da, db, idesc, (kb | k) != 0 ? 1u : 0u);
+        for (int h = 0; h < C::A_TILES; ++h) {
+#pragma unroll
+          for (int k = 0; k < BK / UMMA_K; ++k) {
+            const uint64_t da = make_smem_desc(sa + h * C::A_BYTES + k * UMMA_K * 2);
+            const uint64_t db = make_smem_desc(sb + k * UMMA_K * 2);
+            tc_mma_bf16(tmem_base, da, db, idesc, (kb | k | h) != 0 ? 1u : 0u);
+          }
         }
         tc_commit(empty_bar(s));  // slot reusable once these MMAs have read it
       }
@@ -181,6 +190,7 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1)
     const uint32_t tq = tmem_base + ((uint32_t)(quad * 32) << 16);
     if (EPI == GEMM_SWIGLU_BF16) {
       uint16_t* o = reinterpret_cast<uint16_t*>(out) + (size_t)row * (N / 2) + n0 / 2;
+      uint16_t* ol = out_lo ? reinterpret_cast<uint16_t*>(out_lo) + (size_t)row * (N / 2) + n0 / 2 : nullptr;
 #pragma unroll 1
       for (int blk = 0; blk < BN / 128; ++blk)
 #pragma unroll 1
@@ -190,17 +200,23 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1)
           tc_ld32(tq + blk * 128 + 64 + half * 32, u);
           tc_wait_ld();
           if (row < T) {
-            uint32_t pk[16];
+            uint32_t pk[16], pl[16];
 #pragma unroll
             for (int i = 0; i < 16; ++i) {
               const float g0 = __uint_as_float(g[2 * i]), g1 = __uint_as_float(g[2 * i + 1]);
               const float a0 = g0 / (1.0f + __expf(-g0)) * __uint_as_float(u[2 * i]);
               const float a1 = g1 / (1.0f + __expf(-g1)) * __uint_as_float(u[2 * i + 1]);
               pk[i] = pack_bf16x2(a0, a1);
+              pl[i] = pack_bf16x2(a0 - bf16lo(pk[i]), a1 - bf16hi(pk[i]));
             }
             uint4* dst = reinterpret_cast<uint4*>(o + blk * 64 + half * 32);
 #pragma unroll
             for (int i = 0; i < 4; ++i) dst[i] = make_uint4(pk[4 * i], pk[4 * i + 1], pk[4 * i + 2], pk[4 * i + 3]);
+            if (ol) {
+              uint4* dl = reinterpret_cast<uint4*>(ol + blk * 64 + half * 32);
+#pragma unroll
+              for (int i = 0; i < 4; ++i) dl[i] = make_uint4(pl[4 * i], pl[4 * i + 1], pl[4 * i + 2], pl[4 * i + 3]);
+            }
           }
         }
     } else {
@@ -277,44 +293,55 @@ bool make_map(CUtensorMap* m, const void* ptr, uint64_t rows, uint64_t cols, uin
              CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
 }
 
-template <int BN, int EPI>
-cudaError_t launch_tile(const uint16_t* A, const uint16_t* W, void* out, int T, int N, int K, cudaStream_t s) {
-  CUtensorMap ma, mw;
-  if (!make_map(&ma, A, (uint64_t)T, (uint64_t)K, BM) || !make_map(&mw, W, (uint64_t)N, (uint64_t)K, BN))
+template <int BN, int EPI, bool SPLIT>
+cudaError_t launch_tile(const uint16_t* A, const uint16_t* Alo, const uint16_t* W, void* out, void* out_lo, int T,
+                        int N, int K, cudaStream_t s) {
+  CUtensorMap ma, ml, mw;
+  if (!make_map(&ma, A, (uint64_t)T, (uint64_t)K, BM) || !make_map(&mw, W, (uint64_t)N, (uint64_t)K, BN) ||
+      !make_map(&ml, SPLIT ? Alo : A, (uint64_t)T, (uint64_t)K, BM))
     return cudaErrorInvalidValue;
-  auto kern = gemm_tc_kernel<BN, EPI>;
-  cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, TileCfg<BN>::SMEM);
+  auto kern = gemm_tc_kernel<BN, EPI, SPLIT>;
+  cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, TileCfg<BN, SPLIT>::SMEM);
   if (e != cudaSuccess) return e;
   dim3 grid(N / BN, (T + BM - 1) / BM);
-  kern<<<grid, GEMM_THREADS, TileCfg<BN>::SMEM, s>>>(ma, mw, out, T, N, K);
+  kern<<<grid, GEMM_THREADS, TileCfg<BN, SPLIT>::SMEM, s>>>(ma, ml, mw, out, out_lo, T, N, K);
   return cudaGetLastError();
 }
 
-template <int EPI>
-cudaError_t launch_epi(const uint16_t* A, const uint16_t* W, void* out, int T, int N, int K, cudaStream_t s) {
+template <int EPI, bool SPLIT>
+cudaError_t launch_epi(const uint16_t* A, const uint16_t* Alo, const uint16_t* W, void* out, void* out_lo, int T,
+                       int N, int K, cudaStream_t s) {
   // pick the widest tile that still yields at least ~one wave of CTAs on 148 SMs
   const int mt = (T + BM - 1) / BM;
-  if (N % 256 == 0 && (N / 256) * mt >= 148) return launch_tile<256, EPI>(A, W, out, T, N, K, s);
-  if (EPI == GEMM_SWIGLU_BF16) {
+  if (N % 256 == 0 && (N / 256) * mt >= 148) return launch_tile<256, EPI, SPLIT>(A, Alo, W, out, out_lo, T, N, K, s);
+  if constexpr (EPI == GEMM_SWIGLU_BF16) {
     if (N % 128 != 0) return cudaErrorInvalidValue;
-    return launch_tile<128, EPI>(A, W, out, T, N, K, s);
+    return launch_tile<128, EPI, SPLIT>(A, Alo, W, out, out_lo, T, N, K, s);
+  } else {
+    if (N % 128 == 0 && (N / 128) * mt >= 148) return launch_tile<128, EPI, SPLIT>(A, Alo, W, out, out_lo, T, N, K, s);
+    return launch_tile<64, EPI, SPLIT>(A, Alo, W, out, out_lo, T, N, K, s);
   }
-  if (N % 128 == 0 && (N / 128) * mt >= 148) return launch_tile<128, EPI>(A, W, out, T, N, K, s);
-  return launch_tile<64, EPI>(A, W, out, T, N, K, s);
+}
+
+template <bool SPLIT>
+cudaError_t launch_split(const uint16_t* A, const uint16_t* Alo, const uint16_t* W, void* out, void* out_lo, int T,
+                         int N, int K, int epi, cudaStream_t s) {
+  switch (epi) {
+    case GEMM_STORE_BF16: return launch_epi<GEMM_STORE_BF16, SPLIT>(A, Alo, W, out, out_lo, T, N, K, s);
+    case GEMM_STORE_F32: return launch_epi<GEMM_STORE_F32, SPLIT>(A, Alo, W, out, out_lo, T, N, K, s);
+    case GEMM_RESID_F32: return launch_epi<GEMM_RESID_F32, SPLIT>(A, Alo, W, out, out_lo, T, N, K, s);
+    case GEMM_SWIGLU_BF16: return launch_epi<GEMM_SWIGLU_BF16, SPLIT>(A, Alo, W, out, out_lo, T, N, K, s);
+  }
+  return cudaErrorInvalidValue;
 }
 
 }  // namespace
 
-cudaError_t launch_gemm_tcgen05(const uint16_t* A, const uint16_t* W, void* out, int T, int N, int K, int epi,
-                                cudaStream_t s) {
+cudaError_t launch_gemm_tcgen05(const uint16_t* A, const uint16_t* Alo, const uint16_t* W, void* out, void* out_lo,
+                                int T, int N, int K, int epi, cudaStream_t s) {
   if (K % BK != 0 || T < 1 || N % 64 != 0) return cudaErrorInvalidValue;
-  switch (epi) {
-    case GEMM_STORE_BF16: return launch_epi<GEMM_STORE_BF16>(A, W, out, T, N, K, s);
-    case GEMM_STORE_F32: return launch_epi<GEMM_STORE_F32>(A, W, out, T, N, K, s);
-    case GEMM_RESID_F32: return launch_epi<GEMM_RESID_F32>(A, W, out, T, N, K, s);
-    case GEMM_SWIGLU_BF16: return launch_epi<GEMM_SWIGLU_BF16>(A, W, out, T, N, K, s);
-  }
-  return cudaErrorInvalidValue;
+  return Alo ? launch_split<true>(A, Alo, W, out, out_lo, T, N, K, epi, s)
+             : launch_split<false>(A, Alo, W, out, out_lo, T, N, K, epi, s);
 }
 
 }  // namespace llmc

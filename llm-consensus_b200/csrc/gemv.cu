@@ -5,7 +5,8 @@
 //
 // HBM-bound (W bytes are read once per decode step).  Design:
 //   * one warp owns R rows; each lane streams 16-byte chunks (8 bf16) of those rows with
-//     L1::no_allocate loads, 8 loads in flight per lane while the previous 8 are consumed;
+//     L1::no_allocate loads, two register batches of 8 loads in flight per lane; small matrices
+//     additionally split K over 2 or 4 warps of a block so that more warps stream at once;
 //   * the first batch of weight loads is issued BEFORE griddepcontrol.wait, so under
 //     programmatic dependent launch the weight stream of kernel n+1 overlaps the tail of
 //     kernel n (weights never depend on a previous kernel);
@@ -21,10 +22,14 @@ namespace llmc {
 
 namespace {
 
+// A block has WARPS warps = RG row groups x KS k-slices: warp w works on row group w / KS and on
+// the k-range slice w % KS of its rows; the KS partial sums meet in shared memory.  Splitting K
+// multiplies the number of warps streaming a small matrix (O, QKV, down at batch 1), which is
+// what keeps enough bytes in flight to cover the HBM latency.
 template <int EPI>
 struct GemvCfg {
   static constexpr int R = (EPI == EPI_LMHEAD) ? 4 : 2;       // rows per warp
-  static constexpr int WARPS = (EPI == EPI_LMHEAD || EPI == EPI_SWIGLU) ? 8 : 4;
+  static constexpr int WARPS = 8;
 };
 
 // smem position of element k of a staged activation row (see file header)
@@ -46,14 +51,16 @@ __device__ __forceinline__ float dot8(const uint4& w, const float4& a, const flo
   return s;
 }
 
-template <int EPI, int PRO, int BT>
+template <int EPI, int PRO, int BT, int KS>
 __global__ void __launch_bounds__(GemvCfg<EPI>::WARPS * 32) gemv_kernel(const GemvArgs a) {
   constexpr int R = GemvCfg<EPI>::R;
   constexpr int WARPS = GemvCfg<EPI>::WARPS;
-  constexpr int UK = 8 / R;  // k-iterations per register batch (8 loads in flight per lane)
+  constexpr int RG = WARPS / KS;  // row groups per block
+  constexpr int UK = 8 / R;       // k-iterations per register batch (8 loads per lane per batch, 2 batches in flight)
   extern __shared__ __align__(16) float smem[];
   float* xs = smem;                        // [BT][K] permuted
   float* red = smem + (size_t)BT * a.K;    // [WARPS][BT] sum of squares
+  float* ksum = red + WARPS * BT;          // [WARPS][R][BT] k-slice partial sums
   __shared__ float s_val[WARPS][BT];
   __shared__ int s_idx[WARPS][BT];
   __shared__ bool s_last;
@@ -63,8 +70,12 @@ __global__ void __launch_bounds__(GemvCfg<EPI>::WARPS * 32) gemv_kernel(const Ge
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int K = a.K, NIT = K >> 8;
   const int ngroups = a.N / R;
-  const int g = blockIdx.x * WARPS + warp;
+  const int rg = warp / KS, ks = warp % KS;
+  const int g = blockIdx.x * RG + rg;
   const bool active = g < ngroups;
+  // this warp's k-iterations: [it_lo, it_hi)
+  const int it_per = (NIT + KS - 1) / KS;
+  const int it_lo = ks * it_per, it_hi = min(NIT, it_lo + it_per);
 
   // ---- rows of this warp
   int rows[R];
@@ -84,20 +95,37 @@ __global__ void __launch_bounds__(GemvCfg<EPI>::WARPS * 32) gemv_kernel(const Ge
 #pragma unroll
   for (int r = 0; r < R; ++r) wp[r] = a.W + (size_t)(active ? rows[r] : 0) * K + lane * 8;
 
+  // two register batches of R * UK = 8 loads (128 B per lane, 4 KB per warp) each: batch i+1 is
+  // requested before batch i is consumed.  (A finer-grained rolling refill measured 2x slower:
+  // the 6 scoreboard slots per warp make a consumer wait for the youngest load sharing its slot.)
   uint4 wcur[R][UK], wnxt[R][UK];
   auto load_batch = [&](uint4(&w)[R][UK], int it0) {
 #pragma unroll
     for (int u = 0; u < UK; ++u) {
-      int it = it0 + u;
+      const int it = it0 + u;
 #pragma unroll
       for (int r = 0; r < R; ++r)
-        w[r][u] = (active && it < NIT) ? ldg_stream(wp[r] + (size_t)it * 256) : make_uint4(0, 0, 0, 0);
+        w[r][u] = (active && it < it_hi) ? ldg_stream(wp[r] + (size_t)it * 256) : make_uint4(0, 0, 0, 0);
     }
   };
   // weights do not depend on the previous kernel: start streaming before the dependency wait
-  load_batch(wcur, 0);
+  load_batch(wcur, it_lo);
+  load_batch(wnxt, it_lo + UK);
 
   pdl_wait();
+
+  // epilogue metadata of batch row `lane`, fetched now so that its dependent-load chain
+  // (slot -> position -> page / rope entry) overlaps the weight stream instead of trailing it
+  int e_pos = 0, e_page = 0;
+  float e_cos = 1.f, e_sin = 0.f;
+  if (EPI == EPI_QKV_ROPE && active && ks == 0 && lane < a.B) {
+    const int hd2 = a.head_dim >> 1;
+    const int slot = a.slots[lane];
+    e_pos = a.seq_len[slot];
+    e_page = a.block_table[(size_t)slot * a.bt_stride + e_pos / a.page_size];
+    e_cos = a.rope_cos[(size_t)e_pos * hd2 + (g % hd2)];
+    e_sin = a.rope_sin[(size_t)e_pos * hd2 + (g % hd2)];
+  }
 
   // ---- prologue: stage x (and fold the RMSNorm gain), sum of squares per batch row
   float ss[BT];
@@ -155,17 +183,16 @@ __global__ void __launch_bounds__(GemvCfg<EPI>::WARPS * 32) gemv_kernel(const Ge
 #pragma unroll
     for (int b = 0; b < BT; ++b) acc[r][b] = 0.f;
 
-  for (int it0 = 0; it0 < NIT; it0 += UK) {
-    load_batch(wnxt, it0 + UK);
+  for (int it0 = it_lo; it0 < it_hi; it0 += UK) {
 #pragma unroll
     for (int u = 0; u < UK; ++u) {
-      int it = it0 + u;
-      if (it < NIT) {
+      const int it = it0 + u;
+      if (it < it_hi) {
         const float* xp = xs + (it << 8) + (lane << 2);
 #pragma unroll
         for (int b = 0; b < BT; ++b) {
-          float4 x0 = *reinterpret_cast<const float4*>(xp + (size_t)b * K);
-          float4 x1 = *reinterpret_cast<const float4*>(xp + (size_t)b * K + 128);
+          const float4 x0 = *reinterpret_cast<const float4*>(xp + (size_t)b * K);
+          const float4 x1 = *reinterpret_cast<const float4*>(xp + (size_t)b * K + 128);
 #pragma unroll
           for (int r = 0; r < R; ++r) acc[r][b] += dot8(wcur[r][u], x0, x1);
         }
@@ -175,15 +202,42 @@ __global__ void __launch_bounds__(GemvCfg<EPI>::WARPS * 32) gemv_kernel(const Ge
     for (int u = 0; u < UK; ++u)
 #pragma unroll
       for (int r = 0; r < R; ++r) wcur[r][u] = wnxt[r][u];
+    load_batch(wnxt, it0 + 2 * UK);
   }
 #pragma unroll
   for (int r = 0; r < R; ++r)
 #pragma unroll
-    for (int b = 0; b < BT; ++b) acc[r][b] = warp_sum(acc[r][b]) * rs[b];
+    for (int b = 0; b < BT; ++b) acc[r][b] = warp_sum(acc[r][b]);
+  if (KS > 1) {
+    // combine the k-slices: every warp publishes, the slice-0 warp of each row group sums
+    if (lane == 0) {
+#pragma unroll
+      for (int r = 0; r < R; ++r)
+#pragma unroll
+        for (int b = 0; b < BT; ++b) ksum[(warp * R + r) * BT + b] = acc[r][b];
+    }
+    __syncthreads();
+    if (ks == 0) {
+#pragma unroll
+      for (int r = 0; r < R; ++r)
+#pragma unroll
+        for (int b = 0; b < BT; ++b) {
+          float t = 0.f;
+#pragma unroll
+          for (int k2 = 0; k2 < KS; ++k2) t += ksum[((warp + k2) * R + r) * BT + b];
+          acc[r][b] = t;
+        }
+    }
+  }
+  const bool owner = active && ks == 0;   // the warp that finishes this row group
+#pragma unroll
+  for (int r = 0; r < R; ++r)
+#pragma unroll
+    for (int b = 0; b < BT; ++b) acc[r][b] *= rs[b];
 
   // ---- epilogues: after the butterfly every lane holds every sum; lane b finishes batch row b
   if (EPI == EPI_STORE || EPI == EPI_RESID) {
-    if (active && lane < a.B) {
+    if (owner && lane < a.B) {
 #pragma unroll
       for (int b = 0; b < BT; ++b)
         if (lane == b) {
@@ -195,7 +249,7 @@ __global__ void __launch_bounds__(GemvCfg<EPI>::WARPS * 32) gemv_kernel(const Ge
         }
     }
   } else if (EPI == EPI_SWIGLU) {
-    if (active && lane < a.B) {
+    if (owner && lane < a.B) {
 #pragma unroll
       for (int b = 0; b < BT; ++b)
         if (lane == b) {
@@ -204,18 +258,16 @@ __global__ void __launch_bounds__(GemvCfg<EPI>::WARPS * 32) gemv_kernel(const Ge
         }
     }
   } else if (EPI == EPI_QKV_ROPE) {
-    if (active && lane < a.B) {
+    if (owner && lane < a.B) {
       const int d = a.head_dim, hd2 = d >> 1;
       const int h = g / hd2, i = g - h * hd2;
 #pragma unroll
       for (int b = 0; b < BT; ++b)
         if (lane == b) {
-          const int slot = a.slots[b];
-          const int pos = a.seq_len[slot];
+          const int pos = e_pos;
           float v0 = acc[0][b], v1 = acc[1][b];
           if (h < a.q_heads + a.kv_heads) {
-            float c = a.rope_cos[(size_t)pos * hd2 + i], s = a.rope_sin[(size_t)pos * hd2 + i];
-            float o0 = v0 * c - v1 * s, o1 = v1 * c + v0 * s;
+            const float o0 = v0 * e_cos - v1 * e_sin, o1 = v1 * e_cos + v0 * e_sin;
             v0 = o0; v1 = o1;
           }
           if (h < a.q_heads) {
@@ -225,12 +277,18 @@ __global__ void __launch_bounds__(GemvCfg<EPI>::WARPS * 32) gemv_kernel(const Ge
           } else {
             const bool isk = h < a.q_heads + a.kv_heads;
             const int kvh = isk ? h - a.q_heads : h - a.q_heads - a.kv_heads;
-            const int page = a.block_table[(size_t)slot * a.bt_stride + pos / a.page_size];
+            const int page = e_page;
             const int off = pos % a.page_size;
-            uint16_t* dst = (isk ? a.kpool : a.vpool) +
-                            (((size_t)page * a.kv_heads + kvh) * a.page_size + off) * d + i;
-            dst[0] = f32_to_bf16_bits(v0);
-            dst[hd2] = f32_to_bf16_bits(v1);
+            const size_t eo = (((size_t)page * a.kv_heads + kvh) * a.page_size + off) * d + i;
+            if (a.kv_fp32) {
+              float* dst = reinterpret_cast<float*>(isk ? a.kpool : a.vpool) + eo;
+              dst[0] = v0;
+              dst[hd2] = v1;
+            } else {
+              uint16_t* dst = reinterpret_cast<uint16_t*>(isk ? a.kpool : a.vpool) + eo;
+              dst[0] = f32_to_bf16_bits(v0);
+              dst[hd2] = f32_to_bf16_bits(v1);
+            }
           }
         }
     }
@@ -242,7 +300,7 @@ __global__ void __launch_bounds__(GemvCfg<EPI>::WARPS * 32) gemv_kernel(const Ge
         if (lane == b) {
           float best = -INFINITY;
           int bi = 0x7fffffff;
-          if (active && b < a.B) {
+          if (owner && b < a.B) {
 #pragma unroll
             for (int r = 0; r < R; ++r) {
               float v = acc[r][b];
@@ -305,13 +363,13 @@ __global__ void __launch_bounds__(GemvCfg<EPI>::WARPS * 32) gemv_kernel(const Ge
   }
 }
 
-template <int EPI, int PRO, int BT>
-cudaError_t launch_one(const GemvArgs& a, bool pdl, cudaStream_t s) {
-  constexpr int R = GemvCfg<EPI>::R, WARPS = GemvCfg<EPI>::WARPS;
+template <int EPI, int PRO, int BT, int KS>
+cudaError_t launch_ks(const GemvArgs& a, bool pdl, cudaStream_t s) {
+  constexpr int R = GemvCfg<EPI>::R, WARPS = GemvCfg<EPI>::WARPS, RG = WARPS / KS;
   const int ngroups = a.N / R;
-  const int grid = (ngroups + WARPS - 1) / WARPS;
-  const size_t smem = ((size_t)BT * a.K + (size_t)WARPS * BT) * sizeof(float);
-  auto kern = gemv_kernel<EPI, PRO, BT>;
+  const int grid = (ngroups + RG - 1) / RG;
+  const size_t smem = ((size_t)BT * a.K + (size_t)WARPS * BT + (size_t)WARPS * R * BT) * sizeof(float);
+  auto kern = gemv_kernel<EPI, PRO, BT, KS>;
   if (smem > 48 * 1024) {
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
@@ -329,6 +387,23 @@ cudaError_t launch_one(const GemvArgs& a, bool pdl, cudaStream_t s) {
   return cudaLaunchKernelEx(&cfg, kern, a);
 }
 
+// k-slices per row group: enough warps to keep ~4096 row-group tasks in flight on small matrices
+int pick_ks(int N, int K, int R) {
+  const int tasks = N / R, nit = K >> 8;
+  int ks = 1;
+  while (ks < 4 && tasks * ks < 4096 && R * nit / (ks * 2) >= 8) ks *= 2;   // keep >= 8 loads per lane
+  return ks;
+}
+
+template <int EPI, int PRO, int BT>
+cudaError_t launch_one(const GemvArgs& a, bool pdl, cudaStream_t s) {
+  switch (pick_ks(a.N, a.K, GemvCfg<EPI>::R)) {
+    case 1: return launch_ks<EPI, PRO, BT, 1>(a, pdl, s);
+    case 2: return launch_ks<EPI, PRO, BT, 2>(a, pdl, s);
+    default: return launch_ks<EPI, PRO, BT, 4>(a, pdl, s);
+  }
+}
+
 template <int EPI, int PRO>
 cudaError_t launch_bt(int bt, const GemvArgs& a, bool pdl, cudaStream_t s) {
   switch (bt) {
@@ -343,8 +418,9 @@ cudaError_t launch_bt(int bt, const GemvArgs& a, bool pdl, cudaStream_t s) {
 }  // namespace
 
 int gemv_lmhead_blocks(int N) {
-  constexpr int R = GemvCfg<EPI_LMHEAD>::R, WARPS = GemvCfg<EPI_LMHEAD>::WARPS;
-  return (N / R + WARPS - 1) / WARPS;
+  // upper bound over the k-split choices (RG >= WARPS / 4)
+  constexpr int R = GemvCfg<EPI_LMHEAD>::R, RG = GemvCfg<EPI_LMHEAD>::WARPS / 4;
+  return (N / R + RG - 1) / RG;
 }
 
 cudaError_t launch_gemv(int epi, int pro, int bt, const GemvArgs& a, bool pdl, cudaStream_t s) {

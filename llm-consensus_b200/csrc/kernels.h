@@ -39,8 +39,9 @@ struct GemvArgs {
   const int* seq_len;     // [max_slots] tokens already in the cache = position of the new token
   const int* block_table; // [max_slots][bt_stride] page ids
   int bt_stride;
-  uint16_t* kpool;        // this layer's K pages [page][kv_head][page_size][head_dim]
-  uint16_t* vpool;
+  void* kpool;            // this layer's K pages [page][kv_head][page_size][head_dim], bf16 or fp32
+  void* vpool;
+  int kv_fp32;
   int page_size, q_heads, kv_heads, head_dim;
   // LMHEAD (greedy argmax, lowest index wins ties; last block finalises the step)
   float* part_val;        // [B][gridDim.x]
@@ -63,8 +64,9 @@ int gemv_lmhead_blocks(int N);
 struct AttnDecodeArgs {
   const float* q;          // [B][q_heads*head_dim] fp32 (RoPE applied)
   float* out;              // [B][q_heads*head_dim] fp32
-  const uint16_t* kpool;   // this layer's pages [page][kv_head][page_size][head_dim] bf16
-  const uint16_t* vpool;
+  const void* kpool;       // this layer's pages [page][kv_head][page_size][head_dim], bf16 or fp32
+  const void* vpool;
+  int kv_fp32;
   const int* slots;        // [B]
   const int* seq_len;      // [max_slots]; context length used = seq_len + ctx_extra
   int ctx_extra;           // 1 during decode (the token appended by this step's QKV kernel)
@@ -77,33 +79,38 @@ struct AttnDecodeArgs {
 };
 cudaError_t launch_attn_decode(const AttnDecodeArgs& a, bool pdl, cudaStream_t s);
 size_t attn_decode_scratch_floats(int B, int q_heads, int nsplit, int head_dim);
-int attn_decode_default_nsplit(int B, int kv_heads);
+constexpr int ATTN_MAX_SPLIT = 8;
+// blocks per (sequence, kv head) for a batch whose longest context is max_ctx_tokens
+int attn_decode_nsplit(int max_ctx_tokens);
 
 // ------------------------------------------------------------------ prefill.cu
 cudaError_t launch_embed_rows(const uint16_t* emb, const int* tokens, int T, int H, float* x, cudaStream_t s);
-cudaError_t launch_rmsnorm_rows(const float* x, const uint16_t* gain, float eps, int T, int H, uint16_t* out_bf16,
-                                cudaStream_t s);
-// qkv fp32 [T][qd+2kd] -> q bf16 [T][qd] (RoPE), k/v appended to the pages at positions p0..p0+T-1
+// RMSNorm of fp32 rows -> bf16 GEMM operand.  out_lo != NULL: split form, x = hi + lo with both bf16
+// (the pair carries 16 mantissa bits; the GEMM then accumulates A_hi W + A_lo W).
+cudaError_t launch_rmsnorm_rows(const float* x, const uint16_t* gain, float eps, int T, int H, uint16_t* out_hi,
+                                uint16_t* out_lo, cudaStream_t s);
+// qkv fp32 [T][qd+2kd] -> q fp32 [T][qd] (RoPE), k/v appended to the pages at positions p0..p0+T-1
 cudaError_t launch_rope_append(const float* qkv, int T, int p0, int slot, const float* rope_cos,
-                               const float* rope_sin, const int* block_table, int bt_stride, uint16_t* kpool,
-                               uint16_t* vpool, int page_size, int q_heads, int kv_heads, int head_dim,
-                               uint16_t* q_out, cudaStream_t s);
-// causal attention of T new rows (positions p0..p0+T-1) over the paged cache; out bf16 [T][qd]
-cudaError_t launch_prefill_attention(const uint16_t* q, int T, int p0, int slot, const int* block_table,
-                                     int bt_stride, const uint16_t* kpool, const uint16_t* vpool, int page_size,
-                                     int q_heads, int kv_heads, int head_dim, uint16_t* out, cudaStream_t s);
+                               const float* rope_sin, const int* block_table, int bt_stride, void* kpool,
+                               void* vpool, int kv_fp32, int page_size, int q_heads, int kv_heads, int head_dim,
+                               float* q_out, cudaStream_t s);
+// causal attention of T new rows (positions p0..p0+T-1) over the paged cache; out bf16 [T][qd] (hi, lo)
+cudaError_t launch_prefill_attention(const float* q, int T, int p0, int slot, const int* block_table,
+                                     int bt_stride, const void* kpool, const void* vpool, int kv_fp32, int page_size,
+                                     int q_heads, int kv_heads, int head_dim, uint16_t* out_hi, uint16_t* out_lo,
+                                     cudaStream_t s);
 
 // ------------------------------------------------------------------ gemm_tcgen05.cu / gemm_simple.cu (prefill)
-// C[T][N] = A[T][K] (bf16) * W[N][K]^T (bf16), fp32 accumulation.
+// C[T][N] = (A_hi [+ A_lo])[T][K] (bf16) * W[N][K]^T (bf16), fp32 accumulation.  A_lo may be NULL.
 enum GemmEpi {
   GEMM_STORE_BF16 = 0,  // out bf16 [T][N]
   GEMM_STORE_F32 = 1,   // out f32  [T][N]
   GEMM_RESID_F32 = 2,   // out f32  [T][N] += acc
-  GEMM_SWIGLU_BF16 = 3  // W rows gate/up interleaved in blocks of 64; out bf16 [T][N/2] = silu(g)*u
+  GEMM_SWIGLU_BF16 = 3  // W rows gate/up interleaved in blocks of 64; out bf16 [T][N/2] = silu(g)*u (hi [, lo])
 };
-cudaError_t launch_gemm_tcgen05(const uint16_t* A, const uint16_t* W, void* out, int T, int N, int K, int epi,
-                                cudaStream_t s);
-cudaError_t launch_gemm_simple(const uint16_t* A, const uint16_t* W, void* out, int T, int N, int K, int epi,
-                               cudaStream_t s);
+cudaError_t launch_gemm_tcgen05(const uint16_t* A_hi, const uint16_t* A_lo, const uint16_t* W, void* out,
+                                void* out_lo, int T, int N, int K, int epi, cudaStream_t s);
+cudaError_t launch_gemm_simple(const uint16_t* A_hi, const uint16_t* A_lo, const uint16_t* W, void* out,
+                               void* out_lo, int T, int N, int K, int epi, cudaStream_t s);
 
 }  // namespace llmc

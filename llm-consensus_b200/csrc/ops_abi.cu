@@ -170,39 +170,45 @@ int llmc_op_lmhead(int device, int V, int K, int B, const uint16_t* W, const flo
 }
 
 int llmc_op_attn_decode(int device, int B, int q_heads, int kv_heads, int head_dim, int page_size, int nsplit,
-                        int max_ctx, const int32_t* ctx, const float* q, const uint16_t* k, const uint16_t* v,
+                        int max_ctx, int kv_fp32, const int32_t* ctx, const float* q, const void* k, const void* v,
                         float* out) {
   if (!ctx || !q || !k || !v || !out || B < 1 || kv_heads < 1 || page_size < 32 || page_size % 32)
     return ofail(LLMC_ERR_INVALID, "llmc_op_attn_decode: bad argument");
   O_TRY(cudaSetDevice(device));
   const int D = head_dim, KD = kv_heads * D, QD = q_heads * D;
+  const size_t es = kv_fp32 ? 4 : 2;
   const int pps = (max_ctx + page_size - 1) / page_size;
   std::vector<int> bt;
   scrambled_table(B, pps, bt);
   const size_t pool_elems = (size_t)B * pps * KD * page_size;
-  std::vector<uint16_t> hk(pool_elems, 0), hv(pool_elems, 0);
+  // unwritten page slots hold NaN patterns: a kernel that reads past ctx poisons its output
+  std::vector<unsigned char> hk(pool_elems * es, 0xFF), hv(pool_elems * es, 0xFF);
+  const unsigned char* ks = reinterpret_cast<const unsigned char*>(k);
+  const unsigned char* vs = reinterpret_cast<const unsigned char*>(v);
+  int longest = 1;
   for (int b = 0; b < B; ++b) {
     if (ctx[b] < 1 || ctx[b] > max_ctx) return ofail(LLMC_ERR_INVALID, "llmc_op_attn_decode: ctx out of range");
+    if (ctx[b] > longest) longest = ctx[b];
     for (int p = 0; p < ctx[b]; ++p) {
       const int page = bt[(size_t)b * pps + p / page_size], off = p % page_size;
       for (int h = 0; h < kv_heads; ++h) {
         const size_t dst = (((size_t)page * kv_heads + h) * page_size + off) * D;
         const size_t src = ((size_t)b * max_ctx + p) * KD + (size_t)h * D;
-        memcpy(&hk[dst], k + src, (size_t)D * 2);
-        memcpy(&hv[dst], v + src, (size_t)D * 2);
+        memcpy(&hk[dst * es], ks + src * es, (size_t)D * es);
+        memcpy(&hv[dst * es], vs + src * es, (size_t)D * es);
       }
     }
   }
-  if (nsplit <= 0) nsplit = attn_decode_default_nsplit(B, kv_heads);
+  if (nsplit <= 0) nsplit = attn_decode_nsplit(longest);
   Pool pool;
-  uint16_t *dk, *dv;
+  unsigned char *dk, *dv;
   float *dq, *dout, *scratch;
   int *dbt, *dslots, *dseq;
   unsigned* ctrs;
   std::vector<int> slots(B);
   for (int b = 0; b < B; ++b) slots[b] = b;
-  O_TRY(pool.get(&dk, pool_elems, hk.data()));
-  O_TRY(pool.get(&dv, pool_elems, hv.data()));
+  O_TRY(pool.get(&dk, pool_elems * es, hk.data()));
+  O_TRY(pool.get(&dv, pool_elems * es, hv.data()));
   O_TRY(pool.get(&dq, (size_t)B * QD, q));
   O_TRY(pool.get(&dout, (size_t)B * QD));
   O_TRY(pool.get(&scratch, attn_decode_scratch_floats(B, q_heads, nsplit, D)));
@@ -212,7 +218,8 @@ int llmc_op_attn_decode(int device, int B, int q_heads, int kv_heads, int head_d
   O_TRY(pool.get(&ctrs, (size_t)B * kv_heads));
   AttnDecodeArgs a;
   memset(&a, 0, sizeof(a));
-  a.q = dq; a.out = dout; a.kpool = dk; a.vpool = dv; a.slots = dslots; a.seq_len = dseq; a.ctx_extra = 0;
+  a.q = dq; a.out = dout; a.kpool = dk; a.vpool = dv; a.kv_fp32 = kv_fp32;
+  a.slots = dslots; a.seq_len = dseq; a.ctx_extra = 0;
   a.block_table = dbt; a.bt_stride = pps; a.page_size = page_size;
   a.q_heads = q_heads; a.kv_heads = kv_heads; a.head_dim = D; a.B = B; a.nsplit = nsplit;
   a.scratch = scratch; a.counters = ctrs;
@@ -226,8 +233,8 @@ int llmc_op_attn_decode(int device, int B, int q_heads, int kv_heads, int head_d
   return LLMC_OK;
 }
 
-int llmc_op_gemm(int device, int impl, int epi, int T, int N, int K, const uint16_t* A, const uint16_t* W,
-                 void* out) {
+int llmc_op_gemm(int device, int impl, int epi, int T, int N, int K, const uint16_t* A, const uint16_t* A_lo,
+                 const uint16_t* W, void* out, void* out_lo) {
   if (!A || !W || !out || T < 1) return ofail(LLMC_ERR_INVALID, "llmc_op_gemm: bad argument");
   O_TRY(cudaSetDevice(device));
   Pool pool;
@@ -245,51 +252,60 @@ int llmc_op_gemm(int device, int impl, int epi, int T, int N, int K, const uint1
   }
   const size_t out_cols = epi == GEMM_SWIGLU_BF16 ? N / 2 : N;
   const size_t out_bytes = (size_t)T * out_cols * ((epi == GEMM_STORE_F32 || epi == GEMM_RESID_F32) ? 4 : 2);
-  uint16_t *dA, *dW;
-  unsigned char* dout;
+  uint16_t *dA, *dAl = nullptr, *dW;
+  unsigned char *dout, *dol = nullptr;
   O_TRY(pool.get(&dA, (size_t)T * K, A));
+  if (A_lo) O_TRY(pool.get(&dAl, (size_t)T * K, A_lo));
   O_TRY(pool.get(&dW, (size_t)N * K, hw));
   O_TRY(pool.get(&dout, out_bytes, epi == GEMM_RESID_F32 ? out : nullptr));
-  if (impl == 0) O_TRY(launch_gemm_tcgen05(dA, dW, dout, T, N, K, epi, 0));
-  else O_TRY(launch_gemm_simple(dA, dW, dout, T, N, K, epi, 0));
+  if (out_lo && epi == GEMM_SWIGLU_BF16) O_TRY(pool.get(&dol, out_bytes));
+  if (impl == 0) O_TRY(launch_gemm_tcgen05(dA, dAl, dW, dout, dol, T, N, K, epi, 0));
+  else O_TRY(launch_gemm_simple(dA, dAl, dW, dout, dol, T, N, K, epi, 0));
   O_TRY(cudaDeviceSynchronize());
   O_TRY(cudaMemcpy(out, dout, out_bytes, cudaMemcpyDeviceToHost));
+  if (dol) O_TRY(cudaMemcpy(out_lo, dol, out_bytes, cudaMemcpyDeviceToHost));
   return LLMC_OK;
 }
 
-int llmc_op_rmsnorm_rows(int device, int T, int H, const float* x, const uint16_t* gain, float eps, uint16_t* out) {
+int llmc_op_rmsnorm_rows(int device, int T, int H, const float* x, const uint16_t* gain, float eps, uint16_t* out,
+                         uint16_t* out_lo) {
   if (!x || !gain || !out || T < 1 || H % 8) return ofail(LLMC_ERR_INVALID, "llmc_op_rmsnorm_rows: bad argument");
   O_TRY(cudaSetDevice(device));
   Pool pool;
   float* dx;
-  uint16_t *dg, *dout;
+  uint16_t *dg, *dout, *dlo = nullptr;
   O_TRY(pool.get(&dx, (size_t)T * H, x));
   O_TRY(pool.get(&dg, (size_t)H, gain));
   O_TRY(pool.get(&dout, (size_t)T * H));
-  O_TRY(launch_rmsnorm_rows(dx, dg, eps, T, H, dout, 0));
+  if (out_lo) O_TRY(pool.get(&dlo, (size_t)T * H));
+  O_TRY(launch_rmsnorm_rows(dx, dg, eps, T, H, dout, dlo, 0));
   O_TRY(cudaDeviceSynchronize());
   O_TRY(cudaMemcpy(out, dout, (size_t)T * H * 2, cudaMemcpyDeviceToHost));
+  if (out_lo) O_TRY(cudaMemcpy(out_lo, dlo, (size_t)T * H * 2, cudaMemcpyDeviceToHost));
   return LLMC_OK;
 }
 
 int llmc_op_prefill_attention(int device, int T, int p0, int q_heads, int kv_heads, int head_dim, int page_size,
-                              float rope_theta, const float* qkv, const uint16_t* k_past, const uint16_t* v_past,
-                              uint16_t* out, uint16_t* q_out, uint16_t* k_new, uint16_t* v_new) {
+                              float rope_theta, int kv_fp32, const float* qkv, const void* k_past, const void* v_past,
+                              uint16_t* out, uint16_t* out_lo, float* q_out, void* k_new, void* v_new) {
   if (!qkv || !out || T < 1 || p0 < 0 || (p0 > 0 && (!k_past || !v_past)) || page_size < 32 || page_size % 32)
     return ofail(LLMC_ERR_INVALID, "llmc_op_prefill_attention: bad argument");
   O_TRY(cudaSetDevice(device));
   const int D = head_dim, KD = kv_heads * D, QD = q_heads * D, total = p0 + T;
+  const size_t es = kv_fp32 ? 4 : 2;
   const int pps = (total + page_size - 1) / page_size;
   std::vector<int> bt;
   scrambled_table(1, pps, bt);
   const size_t pool_elems = (size_t)pps * KD * page_size;
-  std::vector<uint16_t> hk(pool_elems, 0), hv(pool_elems, 0);
+  std::vector<unsigned char> hk(pool_elems * es, 0xFF), hv(pool_elems * es, 0xFF);
+  const unsigned char* kps = reinterpret_cast<const unsigned char*>(k_past);
+  const unsigned char* vps = reinterpret_cast<const unsigned char*>(v_past);
   for (int p = 0; p < p0; ++p) {
     const int page = bt[p / page_size], off = p % page_size;
     for (int h = 0; h < kv_heads; ++h) {
       const size_t dst = (((size_t)page * kv_heads + h) * page_size + off) * D;
-      memcpy(&hk[dst], k_past + (size_t)p * KD + (size_t)h * D, (size_t)D * 2);
-      memcpy(&hv[dst], v_past + (size_t)p * KD + (size_t)h * D, (size_t)D * 2);
+      memcpy(&hk[dst * es], kps + ((size_t)p * KD + (size_t)h * D) * es, (size_t)D * es);
+      memcpy(&hv[dst * es], vps + ((size_t)p * KD + (size_t)h * D) * es, (size_t)D * es);
     }
   }
   std::vector<float> hc((size_t)total * (D / 2)), hs((size_t)total * (D / 2));
@@ -300,31 +316,35 @@ int llmc_op_prefill_attention(int device, int T, int p0, int q_heads, int kv_hea
       hs[(size_t)p * (D / 2) + i] = (float)sin(a);
     }
   Pool pool;
-  uint16_t *dk, *dv, *dq, *dout;
-  float *dqkv, *dc, *ds;
+  unsigned char *dk, *dv;
+  uint16_t *dout, *dlo = nullptr;
+  float *dqkv, *dq, *dc, *ds;
   int* dbt;
-  O_TRY(pool.get(&dk, pool_elems, hk.data()));
-  O_TRY(pool.get(&dv, pool_elems, hv.data()));
+  O_TRY(pool.get(&dk, pool_elems * es, hk.data()));
+  O_TRY(pool.get(&dv, pool_elems * es, hv.data()));
   O_TRY(pool.get(&dqkv, (size_t)T * (QD + 2 * KD), qkv));
   O_TRY(pool.get(&dq, (size_t)T * QD));
   O_TRY(pool.get(&dout, (size_t)T * QD));
+  if (out_lo) O_TRY(pool.get(&dlo, (size_t)T * QD));
   O_TRY(pool.get(&dc, hc.size(), hc.data()));
   O_TRY(pool.get(&ds, hs.size(), hs.data()));
   O_TRY(pool.get(&dbt, bt.size(), bt.data()));
-  O_TRY(launch_rope_append(dqkv, T, p0, 0, dc, ds, dbt, pps, dk, dv, page_size, q_heads, kv_heads, D, dq, 0));
-  O_TRY(launch_prefill_attention(dq, T, p0, 0, dbt, pps, dk, dv, page_size, q_heads, kv_heads, D, dout, 0));
+  O_TRY(launch_rope_append(dqkv, T, p0, 0, dc, ds, dbt, pps, dk, dv, kv_fp32, page_size, q_heads, kv_heads, D, dq, 0));
+  O_TRY(launch_prefill_attention(dq, T, p0, 0, dbt, pps, dk, dv, kv_fp32, page_size, q_heads, kv_heads, D, dout, dlo, 0));
   O_TRY(cudaDeviceSynchronize());
   O_TRY(cudaMemcpy(out, dout, (size_t)T * QD * 2, cudaMemcpyDeviceToHost));
-  if (q_out) O_TRY(cudaMemcpy(q_out, dq, (size_t)T * QD * 2, cudaMemcpyDeviceToHost));
+  if (out_lo) O_TRY(cudaMemcpy(out_lo, dlo, (size_t)T * QD * 2, cudaMemcpyDeviceToHost));
+  if (q_out) O_TRY(cudaMemcpy(q_out, dq, (size_t)T * QD * 4, cudaMemcpyDeviceToHost));
   if (k_new || v_new) {
-    O_TRY(cudaMemcpy(hk.data(), dk, pool_elems * 2, cudaMemcpyDeviceToHost));
-    O_TRY(cudaMemcpy(hv.data(), dv, pool_elems * 2, cudaMemcpyDeviceToHost));
+    O_TRY(cudaMemcpy(hk.data(), dk, pool_elems * es, cudaMemcpyDeviceToHost));
+    O_TRY(cudaMemcpy(hv.data(), dv, pool_elems * es, cudaMemcpyDeviceToHost));
     for (int t = 0; t < T; ++t) {
       const int p = p0 + t, page = bt[p / page_size], off = p % page_size;
       for (int h = 0; h < kv_heads; ++h) {
         const size_t src = (((size_t)page * kv_heads + h) * page_size + off) * D;
-        if (k_new) memcpy(k_new + (size_t)t * KD + (size_t)h * D, &hk[src], (size_t)D * 2);
-        if (v_new) memcpy(v_new + (size_t)t * KD + (size_t)h * D, &hv[src], (size_t)D * 2);
+        const size_t dst = (size_t)t * KD + (size_t)h * D;
+        if (k_new) memcpy(reinterpret_cast<unsigned char*>(k_new) + dst * es, &hk[src * es], (size_t)D * es);
+        if (v_new) memcpy(reinterpret_cast<unsigned char*>(v_new) + dst * es, &hv[src * es], (size_t)D * es);
       }
     }
   }
@@ -375,7 +395,7 @@ int64_t llmc_debug_tensor(llmc_engine* e, int layer, int kind, uint16_t* out, in
   return n;
 }
 
-int llmc_debug_kv(llmc_engine* e, int slot, int layer, int pos, uint16_t* k, uint16_t* v) {
+int llmc_debug_kv(llmc_engine* e, int slot, int layer, int pos, void* k, void* v) {
   if (!e || !k || !v) return LLMC_ERR_INVALID;
   std::lock_guard<std::mutex> lk(e->mu);
   const ModelDims& d = e->d;
@@ -384,11 +404,14 @@ int llmc_debug_kv(llmc_engine* e, int slot, int layer, int pos, uint16_t* k, uin
   if (cudaSetDevice(e->device) != cudaSuccess) return LLMC_ERR_CUDA;
   cudaStreamSynchronize(e->stream);
   const int D = d.head_dim;
+  const size_t es = e->kv_elem;
   const int page = e->h_block_table[(size_t)slot * e->pages_per_seq + pos / e->page_size], off = pos % e->page_size;
   for (int h = 0; h < d.kv_heads; ++h) {
     const size_t src = (size_t)layer * e->kv_layer_stride + (((size_t)page * d.kv_heads + h) * e->page_size + off) * D;
-    if (cudaMemcpy(k + (size_t)h * D, e->kpool + src, (size_t)D * 2, cudaMemcpyDeviceToHost) != cudaSuccess ||
-        cudaMemcpy(v + (size_t)h * D, e->vpool + src, (size_t)D * 2, cudaMemcpyDeviceToHost) != cudaSuccess)
+    if (cudaMemcpy(reinterpret_cast<unsigned char*>(k) + (size_t)h * D * es, e->kpool + src * es, (size_t)D * es,
+                   cudaMemcpyDeviceToHost) != cudaSuccess ||
+        cudaMemcpy(reinterpret_cast<unsigned char*>(v) + (size_t)h * D * es, e->vpool + src * es, (size_t)D * es,
+                   cudaMemcpyDeviceToHost) != cudaSuccess)
       return LLMC_ERR_CUDA;
   }
   return LLMC_OK;

@@ -13,7 +13,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "lib", "libllmc.so")
 
 SHAPE_CUSTOM, SHAPE_LLAMA_1B, SHAPE_LLAMA_8B = 0, 1, 2
-FLAG_NO_GRAPH, FLAG_NO_PDL = 1, 2
+FLAG_NO_GRAPH, FLAG_NO_PDL, FLAG_KV_BF16, FLAG_PREFILL_BF16 = 1, 2, 4, 8
 OK, ERR_INVALID, ERR_CUDA, ERR_OOM, ERR_STATE, ERR_LIMIT = 0, -1, -2, -3, -4, -5
 
 # every symbol the headers declare (checked by tests/test_abi_symbols.py)
@@ -79,10 +79,10 @@ def lib():
         l.llmc_op_gemv.argtypes = [C.c_int] * 4 + [vp, vp, C.c_int, vp, C.c_float, C.c_int, vp]
         l.llmc_op_gemv_swiglu.argtypes = [C.c_int] * 4 + [vp, vp, vp, vp, C.c_float, vp]
         l.llmc_op_lmhead.argtypes = [C.c_int] * 4 + [vp, vp, vp, C.c_float, vp, vp]
-        l.llmc_op_attn_decode.argtypes = [C.c_int] * 8 + [vp] * 5
-        l.llmc_op_gemm.argtypes = [C.c_int] * 6 + [vp, vp, vp]
-        l.llmc_op_rmsnorm_rows.argtypes = [C.c_int] * 3 + [vp, vp, C.c_float, vp]
-        l.llmc_op_prefill_attention.argtypes = [C.c_int] * 7 + [C.c_float] + [vp] * 7
+        l.llmc_op_attn_decode.argtypes = [C.c_int] * 9 + [vp] * 5
+        l.llmc_op_gemm.argtypes = [C.c_int] * 6 + [vp] * 5
+        l.llmc_op_rmsnorm_rows.argtypes = [C.c_int] * 3 + [vp, vp, C.c_float, vp, vp]
+        l.llmc_op_prefill_attention.argtypes = [C.c_int] * 7 + [C.c_float, C.c_int] + [vp] * 8
         l.llmc_debug_tensor.argtypes = [vp, C.c_int, C.c_int, vp, C.c_int64]
         l.llmc_debug_tensor.restype = C.c_int64
         l.llmc_debug_kv.argtypes = [vp, C.c_int, C.c_int, C.c_int, vp, vp]
@@ -185,9 +185,9 @@ class Engine:
             raise LlmcError(int(n2), "llmc_debug_tensor")
         return out
 
-    def debug_kv(self, slot, layer, pos, kd):
-        k = np.empty(kd, np.uint16)
-        v = np.empty(kd, np.uint16)
+    def debug_kv(self, slot, layer, pos, kd, fp32=True):
+        k = np.empty(kd, np.float32 if fp32 else np.uint16)
+        v = np.empty(kd, np.float32 if fp32 else np.uint16)
         rc = lib().llmc_debug_kv(self.h, slot, layer, pos, k.ctypes.data, v.ctypes.data)
         if rc != OK:
             raise LlmcError(rc, "llmc_debug_kv")
@@ -255,18 +255,23 @@ def op_lmhead(W, x, gain, eps=1e-5, want_logits=True, device=0):
 
 
 def op_attn_decode(q, k, v, ctx, q_heads, kv_heads, head_dim, page_size=64, nsplit=0, device=0):
-    q = _c(q, np.float32); k = _c(k, np.uint16); v = _c(v, np.uint16); ctx = _c(ctx, np.int32)
+    """k, v: uint16 arrays (bf16 bits) or float32 arrays select the KV element type."""
+    kv_fp32 = int(np.asarray(k).dtype == np.float32)
+    dt = np.float32 if kv_fp32 else np.uint16
+    q = _c(q, np.float32); k = _c(k, dt); v = _c(v, dt); ctx = _c(ctx, np.int32)
     B, max_ctx = k.shape[0], k.shape[1]
     out = np.zeros_like(q)
-    _ops_check(lib().llmc_op_attn_decode(device, B, q_heads, kv_heads, head_dim, page_size, nsplit, max_ctx,
+    _ops_check(lib().llmc_op_attn_decode(device, B, q_heads, kv_heads, head_dim, page_size, nsplit, max_ctx, kv_fp32,
                                          ctx.ctypes.data, q.ctypes.data, k.ctypes.data, v.ctypes.data, out.ctypes.data))
     return out
 
 
-def op_gemm(A, W, epi=1, impl=0, out_in=None, device=0):
+def op_gemm(A, W, epi=1, impl=0, out_in=None, A_lo=None, want_lo=False, device=0):
     A = _c(A, np.uint16); W = _c(W, np.uint16)
+    Al = _c(A_lo, np.uint16) if A_lo is not None else None
     T, K = A.shape
     N = W.shape[0]
+    lo = None
     if epi == 0:
         out = np.zeros((T, N), np.uint16)
     elif epi == 1:
@@ -275,28 +280,36 @@ def op_gemm(A, W, epi=1, impl=0, out_in=None, device=0):
         out = _c(out_in, np.float32).copy()
     else:
         out = np.zeros((T, N // 2), np.uint16)
-    _ops_check(lib().llmc_op_gemm(device, impl, epi, T, N, K, A.ctypes.data, W.ctypes.data, out.ctypes.data))
-    return out
+        lo = np.zeros((T, N // 2), np.uint16) if want_lo else None
+    _ops_check(lib().llmc_op_gemm(device, impl, epi, T, N, K, A.ctypes.data, _ptr(Al), W.ctypes.data, out.ctypes.data,
+                                  _ptr(lo)))
+    return (out, lo) if want_lo else out
 
 
-def op_rmsnorm_rows(x, gain, eps=1e-5, device=0):
+def op_rmsnorm_rows(x, gain, eps=1e-5, split=False, device=0):
     x = _c(x, np.float32); g = _c(gain, np.uint16)
     T, H = x.shape
     out = np.zeros((T, H), np.uint16)
-    _ops_check(lib().llmc_op_rmsnorm_rows(device, T, H, x.ctypes.data, g.ctypes.data, eps, out.ctypes.data))
-    return out
+    lo = np.zeros((T, H), np.uint16) if split else None
+    _ops_check(lib().llmc_op_rmsnorm_rows(device, T, H, x.ctypes.data, g.ctypes.data, eps, out.ctypes.data, _ptr(lo)))
+    return (out, lo) if split else out
 
 
-def op_prefill_attention(qkv, k_past, v_past, q_heads, kv_heads, head_dim, page_size=64, rope_theta=500000.0, device=0):
+def op_prefill_attention(qkv, k_past, v_past, q_heads, kv_heads, head_dim, page_size=64, rope_theta=500000.0,
+                         kv_fp32=True, split=True, device=0):
+    """Returns (out_hi, out_lo | None, q fp32, k_new, v_new); k/v arrays are float32 or uint16 (bf16 bits)."""
+    dt = np.float32 if kv_fp32 else np.uint16
     qkv = _c(qkv, np.float32)
     T = qkv.shape[0]
     p0 = 0 if k_past is None else k_past.shape[0]
-    kp = _c(k_past, np.uint16) if p0 else None
-    vp = _c(v_past, np.uint16) if p0 else None
+    kp = _c(k_past, dt) if p0 else None
+    vp = _c(v_past, dt) if p0 else None
     QD, KD = q_heads * head_dim, kv_heads * head_dim
-    out = np.zeros((T, QD), np.uint16); qo = np.zeros((T, QD), np.uint16)
-    kn = np.zeros((T, KD), np.uint16); vn = np.zeros((T, KD), np.uint16)
+    out = np.zeros((T, QD), np.uint16)
+    lo = np.zeros((T, QD), np.uint16) if split else None
+    qo = np.zeros((T, QD), np.float32)
+    kn = np.zeros((T, KD), dt); vn = np.zeros((T, KD), dt)
     _ops_check(lib().llmc_op_prefill_attention(device, T, p0, q_heads, kv_heads, head_dim, page_size, rope_theta,
-                                               qkv.ctypes.data, _ptr(kp), _ptr(vp), out.ctypes.data, qo.ctypes.data,
-                                               kn.ctypes.data, vn.ctypes.data))
-    return out, qo, kn, vn
+                                               int(kv_fp32), qkv.ctypes.data, _ptr(kp), _ptr(vp), out.ctypes.data,
+                                               _ptr(lo), qo.ctypes.data, kn.ctypes.data, vn.ctypes.data))
+    return out, lo, qo, kn, vn

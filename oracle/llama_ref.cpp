@@ -118,6 +118,10 @@ struct Model {
   std::vector<float> kc, vc;
   std::vector<float> rope_cos, rope_sin;  // [max_ctx][head_dim/2]
   int len = 0;
+  // DIAGNOSTIC ONLY (never used by parity tests): emulate bf16 rounding of activations at the
+  // sites where the GPU prefill stores bf16, to attribute the GPU-vs-fp32 logit error.
+  //   1: normalised GEMM inputs  2: q  4: k,v (cache)  8: attention output  16: SwiGLU output
+  int round_mask = 0;
 };
 
 // Y[n,N] (+)= X[n,K] * W[N,K]^T, W bf16 widened to fp32, fp32 accumulation.
@@ -142,6 +146,10 @@ static void linear(const float* X, int n, int K, const uint16_t* W, int N, float
       }
     }
   }
+}
+
+static inline void round_bf16_inplace(float* v, size_t n) {
+  for (size_t i = 0; i < n; ++i) v[i] = bf16_to_f32(bf16_rne(v[i]));
 }
 
 static void rmsnorm(const float* x, const uint16_t* g, int H, float eps, float* y) {
@@ -191,6 +199,7 @@ void* oref_create(const oref_config* cfg) {
 
 void oref_destroy(void* h) { delete (Model*)h; }
 void oref_reset(void* h) { ((Model*)h)->len = 0; }
+void oref_set_round_mask(void* h, int mask) { ((Model*)h)->round_mask = mask; }
 int oref_len(void* h) { return ((Model*)h)->len; }
 // Truncate the context to `len` tokens (cache entries beyond are simply overwritten later).
 void oref_truncate(void* h, int len) {
@@ -242,6 +251,7 @@ int oref_forward(void* h, const int32_t* tokens, int n, int logits_mode, float* 
     float* vc = m->vc.data() + (size_t)l * c.max_ctx * KD;
 #pragma omp parallel for schedule(static)
     for (int t = 0; t < n; ++t) rmsnorm(&x[(size_t)t * H], y.g1.data(), H, c.rms_eps, &hn[(size_t)t * H]);
+    if (m->round_mask & 1) round_bf16_inplace(hn.data(), (size_t)n * H);
     linear(hn.data(), n, H, y.wq.data(), QD, q.data(), QD);
     linear(hn.data(), n, H, y.wk.data(), KD, kc + (size_t)p0 * KD, KD);
     linear(hn.data(), n, H, y.wv.data(), KD, vc + (size_t)p0 * KD, KD);
@@ -258,6 +268,11 @@ int oref_forward(void* h, const int32_t* tokens, int n, int logits_mode, float* 
           v[i + D / 2] = b * cs[i] + a * sn[i];
         }
       }
+    }
+    if (m->round_mask & 2) round_bf16_inplace(q.data(), (size_t)n * QD);
+    if (m->round_mask & 4) {
+      round_bf16_inplace(kc + (size_t)p0 * KD, (size_t)n * KD);
+      round_bf16_inplace(vc + (size_t)p0 * KD, (size_t)n * KD);
     }
     // causal GQA attention, fp32 softmax
 #pragma omp parallel for schedule(dynamic, 4) collapse(2)
@@ -287,10 +302,12 @@ int oref_forward(void* h, const int32_t* tokens, int n, int logits_mode, float* 
           for (int i = 0; i < D; ++i) o[i] += w * vr[i];
         }
       }
+    if (m->round_mask & 8) round_bf16_inplace(att.data(), (size_t)n * QD);
     linear(att.data(), n, QD, y.wo.data(), H, tmp.data(), H);
     for (size_t i = 0; i < (size_t)n * H; ++i) x[i] += tmp[i];
 #pragma omp parallel for schedule(static)
     for (int t = 0; t < n; ++t) rmsnorm(&x[(size_t)t * H], y.g2.data(), H, c.rms_eps, &hn[(size_t)t * H]);
+    if (m->round_mask & 1) round_bf16_inplace(hn.data(), (size_t)n * H);
     linear(hn.data(), n, H, y.wg.data(), I, gate.data(), I);
     linear(hn.data(), n, H, y.wu.data(), I, up.data(), I);
 #pragma omp parallel for schedule(static)
@@ -298,6 +315,7 @@ int oref_forward(void* h, const int32_t* tokens, int n, int logits_mode, float* 
       float g = gate[i];
       gate[i] = g / (1.0f + expf(-g)) * up[i];
     }
+    if (m->round_mask & 16) round_bf16_inplace(gate.data(), (size_t)n * I);
     linear(gate.data(), n, I, y.wd.data(), H, tmp.data(), H);
     for (size_t i = 0; i < (size_t)n * H; ++i) x[i] += tmp[i];
   }

@@ -62,6 +62,7 @@ def lib():
         l.oref_destroy.argtypes = [C.c_void_p]
         l.oref_reset.argtypes = [C.c_void_p]
         l.oref_len.argtypes = [C.c_void_p]
+        l.oref_set_round_mask.argtypes = [C.c_void_p, C.c_int]
         l.oref_truncate.argtypes = [C.c_void_p, C.c_int]
         l.oref_tensor.restype = C.c_int64
         l.oref_tensor.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_int64]
@@ -103,6 +104,10 @@ class Oracle:
 
     def reset(self):
         lib().oref_reset(self.h)
+
+    def set_round_mask(self, mask):
+        """Diagnostic: emulate bf16 storage of activations (see llama_ref.cpp); parity tests use mask 0."""
+        lib().oref_set_round_mask(self.h, mask)
 
     def truncate(self, n):
         lib().oref_truncate(self.h, n)

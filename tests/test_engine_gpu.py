@@ -133,6 +133,37 @@ def test_free_running_greedy_tokens(gpu, name, chunk):
     e.close()
 
 
+@pytest.mark.parametrize("name", ["tiny", "small-d128"])
+@pytest.mark.parametrize("flags", [4, 8, 12])
+def test_reduced_precision_modes(gpu, name, flags):
+    """LLMC_FLAG_KV_BF16 (4) / LLMC_FLAG_PREFILL_BF16 (8): bf16 storage of the KV cache and of the prefill
+    GEMM operands.  On these small shapes the result stays inside the 2e-2 budget; for the KV flag the
+    deviation from the fp32 oracle must moreover be explained by exactly that rounding (the oracle's
+    diagnostic emulation of bf16 KV storage reproduces the GPU logits ~20x more closely than the fp32
+    oracle does); for the prefill flag the emulation is only required not to be worse."""
+    o, e = make_pair(gpu, name, seed=17, flags=flags)
+    V = DIMS[name]["vocab"]
+    prompt = np.random.default_rng(3).integers(0, V, 60)
+    mask = (4 if flags & 4 else 0) | ((1 | 8 | 16) if flags & 8 else 0)
+    slot = e.seq_alloc()
+    nxt, lg = e.prefill(slot, prompt, want_logits=True)
+    exact = o.forward(prompt, "last")
+    o.reset(); o.set_round_mask(mask)
+    emu = o.forward(prompt, "last")
+    err_exact, err_emu = np.abs(lg - exact).max(), np.abs(lg - emu).max()
+    print("flags %d: vs fp32 oracle %.2e, vs storage-rounding emulation %.2e" % (flags, err_exact, err_emu))
+    assert err_exact <= TOL                      # small shapes stay inside the budget even so
+    assert err_emu <= (1e-3 if flags == 4 else max(2e-3, err_exact))
+    # a few decode steps, teacher-forced on the emulation's tokens
+    for s_ in range(6):
+        tok = int(np.argmax(emu))
+        e.set_next_token(slot, tok)
+        _, lgd = e.decode([slot], 1, want_logits=True)
+        emu = o.forward([tok], "last")
+        assert np.abs(lgd[0] - emu).max() <= (1e-3 if flags == 4 else TOL)
+    e.close()
+
+
 def test_chunked_prefill_equals_single_pass(gpu):
     o, e = make_pair(gpu, "tiny", seed=2, prefill_chunk=32)
     _, e2 = make_pair(gpu, "tiny", seed=2, prefill_chunk=2048)
@@ -142,7 +173,7 @@ def test_chunked_prefill_equals_single_pass(gpu):
     n2, l2 = e2.prefill(s2, toks, want_logits=True)
     want = o.forward(toks, "last")
     assert np.abs(l1 - want).max() <= TOL and np.abs(l2 - want).max() <= TOL
-    assert np.abs(l1 - l2).max() <= 5e-3
+    assert np.abs(l1 - l2).max() <= 1e-3
     # split prompt over two llmc_prefill calls (prefix reuse)
     s3 = e.seq_alloc()
     e.prefill(s3, toks[:70])

@@ -84,17 +84,26 @@ def test_lmhead_ties_resolve_to_lowest_index(gpu):
 
 @pytest.mark.parametrize("nq,nkv,d", [(32, 8, 64), (32, 8, 128), (8, 2, 32), (4, 4, 64), (16, 2, 64), (4, 2, 128)])
 @pytest.mark.parametrize("B,ctxs,page,nsplit", [(1, [1], 64, 0), (1, [33], 32, 0), (1, [640], 64, 0), (1, [700], 64, 5),
-                                                  (3, [5, 129, 64], 64, 0), (2, [257, 31], 128, 1)])
-def test_attn_decode(gpu, nq, nkv, d, B, ctxs, page, nsplit):
+                                                  (3, [5, 129, 64], 64, 0), (2, [257, 31], 128, 1), (1, [2500], 64, 0),
+                                                  (2, [3000, 10], 64, 8)])
+@pytest.mark.parametrize("fp32", [True, False])
+def test_attn_decode(gpu, nq, nkv, d, B, ctxs, page, nsplit, fp32):
     rng = np.random.default_rng(nq * d + sum(ctxs))
     max_ctx = ((max(ctxs) + page - 1) // page) * page
     q = rng.standard_normal((B, nq * d)).astype(np.float32)
-    k = rnd_bf16(rng, (B, max_ctx, nkv * d), 1.0)
-    v = rnd_bf16(rng, (B, max_ctx, nkv * d), 1.0)
+    if fp32:
+        k = rng.standard_normal((B, max_ctx, nkv * d)).astype(np.float32)
+        v = rng.standard_normal((B, max_ctx, nkv * d)).astype(np.float32)
+        kf, vf = k, v
+    else:
+        k = rnd_bf16(rng, (B, max_ctx, nkv * d), 1.0)
+        v = rnd_bf16(rng, (B, max_ctx, nkv * d), 1.0)
+        kf, vf = lnp.bf16_to_f32(k), lnp.bf16_to_f32(v)
     got = gpu.op_attn_decode(q, k, v, ctxs, nq, nkv, d, page, nsplit)
+    assert np.isfinite(got).all()
     for b in range(B):
-        kk = lnp.bf16_to_f32(k[b, :ctxs[b]]).reshape(ctxs[b], nkv, d)
-        vv = lnp.bf16_to_f32(v[b, :ctxs[b]]).reshape(ctxs[b], nkv, d)
+        kk = kf[b, :ctxs[b]].reshape(ctxs[b], nkv, d)
+        vv = vf[b, :ctxs[b]].reshape(ctxs[b], nkv, d)
         want = lnp.attention(q[b].reshape(nq, d), kk, vv).reshape(-1)
         close(got[b], want, 2e-4, "attn decode b=%d" % b)
 
@@ -107,42 +116,55 @@ def test_rmsnorm_rows(gpu, T, H):
     got = lnp.bf16_to_f32(gpu.op_rmsnorm_rows(x, gain))
     want = lnp.rmsnorm(x, lnp.bf16_to_f32(gain))
     assert np.abs(got - want).max() <= 2 ** -8 * np.abs(want).max() + 1e-6
+    hi, lo = gpu.op_rmsnorm_rows(x, gain, split=True)                  # hi + lo carries 16 mantissa bits
+    assert np.array_equal(hi, gpu.op_rmsnorm_rows(x, gain))
+    pair = lnp.bf16_to_f32(hi) + lnp.bf16_to_f32(lo)
+    assert np.abs(pair - want).max() <= 2 ** -15 * np.abs(want).max() + 1e-6
 
 
 @pytest.mark.parametrize("nq,nkv,d", [(8, 2, 32), (32, 8, 64), (4, 2, 128), (4, 4, 64)])
 @pytest.mark.parametrize("T,p0,page", [(1, 0, 64), (20, 0, 32), (70, 0, 64), (9, 100, 64), (130, 61, 32)])
-def test_rope_append_and_prefill_attention(gpu, nq, nkv, d, T, p0, page):
+@pytest.mark.parametrize("fp32", [True, False])
+def test_rope_append_and_prefill_attention(gpu, nq, nkv, d, T, p0, page, fp32):
     rng = np.random.default_rng(nq + d + T + p0)
     QD, KD = nq * d, nkv * d
     qkv = rng.standard_normal((T, QD + 2 * KD)).astype(np.float32)
-    kp = rnd_bf16(rng, (p0, KD)) if p0 else None
-    vp = rnd_bf16(rng, (p0, KD)) if p0 else None
-    out, qo, kn, vn = gpu.op_prefill_attention(qkv, kp, vp, nq, nkv, d, page)
+    if fp32:
+        kp = rng.standard_normal((p0, KD)).astype(np.float32) if p0 else None
+        vp = rng.standard_normal((p0, KD)).astype(np.float32) if p0 else None
+        widen = lambda a: a
+    else:
+        kp = rnd_bf16(rng, (p0, KD)) if p0 else None
+        vp = rnd_bf16(rng, (p0, KD)) if p0 else None
+        widen = lnp.bf16_to_f32
+    out, lo, qo, kn, vn = gpu.op_prefill_attention(qkv, kp, vp, nq, nkv, d, page, kv_fp32=fp32, split=True)
     cos, sin = lnp.rope_tables(p0 + T, d)
     pos = np.arange(p0, p0 + T)
     q_want = lnp.rope(qkv[:, :QD].reshape(T, nq, d), pos, cos, sin)
     k_want = lnp.rope(qkv[:, QD:QD + KD].reshape(T, nkv, d), pos, cos, sin)
     v_want = qkv[:, QD + KD:].reshape(T, nkv, d)
-    # q, k, v as stored: one bf16 rounding of the fp32 rotation
-    assert np.array_equal(qo.reshape(T, nq, d), lnp.bf16_rne_bits(q_want).reshape(T, nq, d)) or \
-        np.abs(lnp.bf16_to_f32(qo).reshape(T, nq, d) - q_want).max() <= 2 ** -7 * np.abs(q_want).max()
-    assert np.abs(lnp.bf16_to_f32(kn).reshape(T, nkv, d) - k_want).max() <= 2 ** -7 * np.abs(k_want).max()
-    assert np.array_equal(vn.reshape(T, nkv, d), lnp.bf16_rne_bits(v_want).reshape(T, nkv, d))
+    store_tol = 1e-6 if fp32 else 2 ** -8
+    assert np.abs(qo.reshape(T, nq, d) - q_want).max() <= 1e-6 * np.abs(q_want).max() + 1e-6
+    assert np.abs(widen(kn).reshape(T, nkv, d) - k_want).max() <= store_tol * np.abs(k_want).max() + 1e-6
+    assert np.abs(widen(vn).reshape(T, nkv, d) - v_want).max() <= store_tol * np.abs(v_want).max() + 1e-6
     # attention on exactly what the GPU stored (so only its own arithmetic is under test)
-    k_all = lnp.bf16_to_f32(kn).reshape(T, nkv, d)
-    v_all = lnp.bf16_to_f32(vn).reshape(T, nkv, d)
+    k_all = widen(kn).reshape(T, nkv, d)
+    v_all = widen(vn).reshape(T, nkv, d)
     if p0:
-        k_all = np.concatenate([lnp.bf16_to_f32(kp).reshape(p0, nkv, d), k_all])
-        v_all = np.concatenate([lnp.bf16_to_f32(vp).reshape(p0, nkv, d), v_all])
-    qf = lnp.bf16_to_f32(qo).reshape(T, nq, d)
-    got = lnp.bf16_to_f32(out).reshape(T, nq, d)
+        k_all = np.concatenate([widen(kp).reshape(p0, nkv, d), k_all])
+        v_all = np.concatenate([widen(vp).reshape(p0, nkv, d), v_all])
+    qf = qo.reshape(T, nq, d)
+    hi = lnp.bf16_to_f32(out).reshape(T, nq, d)
+    pair = hi + lnp.bf16_to_f32(lo).reshape(T, nq, d)
     for t in range(T):
         want = lnp.attention(qf[t], k_all[:p0 + t + 1], v_all[:p0 + t + 1])
-        assert np.abs(got[t] - want).max() <= 2 ** -7 * np.abs(want).max() + 1e-4, t
+        assert np.abs(hi[t] - want).max() <= 2 ** -8 * np.abs(want).max() + 1e-4, t
+        assert np.abs(pair[t] - want).max() <= 2e-4 * np.abs(want).max() + 1e-5, t
 
 
-def run_gemm_check(T, N, K, epi, impl, timeout=120):
-    cmd = [sys.executable, os.path.join(ROOT, "tests", "_gemm_tc_check.py")] + [str(v) for v in (T, N, K, epi, impl)]
+def run_gemm_check(T, N, K, epi, impl, split=0, timeout=120):
+    cmd = [sys.executable, os.path.join(ROOT, "tests", "_gemm_tc_check.py")] + \
+        [str(v) for v in (T, N, K, epi, impl, split)]
     r = subprocess.run(cmd, capture_output=True, text=True, timeout=timeout)
     assert r.returncode == 0, "gemm check failed:\n" + r.stdout[-2000:] + r.stderr[-4000:]
     return json.loads(r.stdout.strip().splitlines()[-1])
@@ -152,17 +174,22 @@ GEMM_CASES = [(128, 384, 256, 1), (20, 256, 256, 1), (512, 3072, 2048, 1), (512,
               (512, 16384, 2048, 3), (512, 2048, 8192, 2), (130, 512, 1024, 0), (1024, 6144, 4096, 1)]
 
 
+@pytest.mark.parametrize("split", [0, 1])
 @pytest.mark.parametrize("T,N,K,epi", GEMM_CASES)
-def test_gemm_simple_comparator(gpu, T, N, K, epi):
+def test_gemm_simple_comparator(gpu, T, N, K, epi, split):
     if T * N * K > 2 ** 34:
         pytest.skip("large case only on the tensor-core kernel")
-    r = run_gemm_check(T, N, K, epi, impl=1)
+    r = run_gemm_check(T, N, K, epi, impl=1, split=split)
     assert r["bad_rows"] == 0, r
-    assert r["max_abs"] <= (2 ** -7 if epi in (0, 3) else 1e-4) * r["ref_rms"] * 4 + 1e-5, r
+    assert r["max_excess"] <= 0, r
+    assert r.get("pair_max_excess", 0) <= 0, r
 
 
+@pytest.mark.parametrize("split", [0, 1])
 @pytest.mark.parametrize("T,N,K,epi", GEMM_CASES)
-def test_gemm_tcgen05(gpu, T, N, K, epi):
-    r = run_gemm_check(T, N, K, epi, impl=0)
+def test_gemm_tcgen05(gpu, T, N, K, epi, split):
+    """split=1: the A operand is a bf16 hi+lo pair (the default precision of the engine's prefill)."""
+    r = run_gemm_check(T, N, K, epi, impl=0, split=split)
     assert r["bad_rows"] == 0, r
-    assert r["max_abs"] <= (2 ** -7 if epi in (0, 3) else 1e-4) * r["ref_rms"] * 4 + 1e-5, r
+    assert r["max_excess"] <= 0, r
+    assert r.get("pair_max_excess", 0) <= 0, r
