@@ -65,7 +65,28 @@ def build(force=False, verbose=False):
         r = subprocess.run(cmd, capture_output=True, text=True)
         if r.returncode != 0:
             raise RuntimeError("link failed:\n" + r.stdout + r.stderr)
+    build_host(force or bool(jobs))
     return LIB
+
+
+HOST = os.path.join(HERE, "host")
+HOST_LIB = os.path.join(LIBDIR, "libllmc_host.so")
+CLI = os.path.join(HERE, "bin", "llm-consensus")
+
+
+def build_host(force=False):
+    """The C++ host mirror: libllmc_host.so (test hooks) and the llm-consensus CLI (links libllmc.so)."""
+    os.makedirs(os.path.dirname(CLI), exist_ok=True)
+    srcs = [os.path.join(HOST, f) for f in ("host.cpp", "local_provider.cpp")]
+    deps = srcs + [os.path.join(HOST, f) for f in ("host.hpp", "host_abi.cpp", "main.cpp")] + [LIB]
+    newest = max(os.path.getmtime(d) for d in deps)
+    cxx = ["/usr/bin/g++", "-O2", "-std=c++17", "-Wall", "-fPIC", "-pthread"]
+    link = ["-L" + LIBDIR, "-lllmc", "-Wl,-rpath,$ORIGIN/../lib", "-Wl,-rpath,$ORIGIN"]
+    if force or not os.path.exists(HOST_LIB) or os.path.getmtime(HOST_LIB) < newest:
+        subprocess.check_call(cxx + ["-shared", "-o", HOST_LIB] + srcs + [os.path.join(HOST, "host_abi.cpp")] + link)
+    if force or not os.path.exists(CLI) or os.path.getmtime(CLI) < newest:
+        subprocess.check_call(cxx + ["-o", CLI] + srcs + [os.path.join(HOST, "main.cpp")] + link)
+    return HOST_LIB, CLI
 
 
 if __name__ == "__main__":

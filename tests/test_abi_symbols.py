@@ -23,6 +23,18 @@ def test_every_declared_symbol_is_exported(llmc):
     assert sorted(llmc.OPS_SYMBOLS) == declared("llmc_ops.h")
 
 
+def test_host_library_exports_its_header(llmc):
+    import ctypes
+    import llm_consensus_b200.build as b
+    lib_path, cli = b.build_host()
+    h = ctypes.CDLL(lib_path)
+    names = declared("llmc_host.h")
+    assert len(names) == 5
+    for n in names:
+        assert hasattr(h, n), "libllmc_host.so does not export " + n
+    assert os.access(cli, os.X_OK)
+
+
 def test_no_torch_or_oracle_in_the_product_library(llmc):
     import subprocess
     out = subprocess.run(["ldd", llmc.LIB_PATH], capture_output=True, text=True).stdout

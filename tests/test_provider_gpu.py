@@ -1,0 +1,82 @@
+"""The local provider end to end (GPU): the llm-consensus CLI with local model names -- tokenise,
+prefill + chunked greedy decode through the C ABI, detokenise, judge prompt, result.json -- against the
+same pipeline computed with the CPU oracles (oracle/ref.py for the tokens, oracle/orchestration.py for
+the template and the JSON).  This is BASELINE.json configs[2] in miniature: N seeds of one shape, judge
+over the concatenated responses."""
+import json
+import os
+import re
+import subprocess
+
+import numpy as np
+import pytest
+
+from oracle import orchestration as orc, ref
+
+pytestmark = pytest.mark.gpu
+TINY = ref.SHAPES["tiny"]
+NEW = 12
+
+
+@pytest.fixture(scope="module")
+def cli(gpu):
+    import llm_consensus_b200.build as b
+    return b.build_host()[1]
+
+
+def oracle_answer(seed, prompt_text, n_new=NEW):
+    o = ref.Oracle("tiny", seed=seed, max_ctx=8192)
+    ids = orc.tokenize(prompt_text, TINY["vocab"])
+    toks, lg = o.generate(ids, n_new, want_logits=True)
+    margins = [float(np.sort(l)[-1] - np.sort(l)[-2]) for l in lg]
+    return orc.detokenize(toks.tolist()), min(margins)
+
+
+def test_cli_local_fanout_and_judge_matches_oracle_pipeline(cli):
+    prompt = "What is 2+2?"
+    models = ["local-tiny-s0", "local-tiny-s1", "local-tiny-s2"]
+    r = subprocess.run([cli, "--models", ",".join(models), "--judge", "local-tiny-s0", "--max-new-tokens", str(NEW),
+                        "--json", prompt], capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, r.stderr
+    doc = json.loads(r.stdout)
+    assert doc["prompt"] == prompt and doc["judge"] == "local-tiny-s0"
+    assert sorted(x["model"] for x in doc["responses"]) == models
+    want, margin = {}, {}
+    for i, m in enumerate(models):
+        want[m], margin[m] = oracle_answer(i, prompt)
+    for x in doc["responses"]:
+        assert x["provider"] == "local" and x["latency_ms"] > 0
+        if margin[x["model"]] > 1e-3:                          # no numerical tie among the greedy steps
+            assert x["content"] == want[x["model"]], x["model"]
+    # the judge saw the template rendered over the responses in the order result.json lists them
+    rendered = orc.render_judge_prompt(prompt, doc["responses"])
+    consensus, jm = oracle_answer(0, rendered)
+    if jm > 1e-3:
+        assert doc["consensus"] == consensus
+    # and the whole document is what Go's encoder would have written for these values
+    resps = [dict(x) for x in doc["responses"]]
+    assert r.stdout == orc.encode_result(prompt, resps, doc["consensus"], doc["judge"])
+    # generated text is printable ASCII that re-tokenises to the same ids
+    for x in doc["responses"]:
+        ids = orc.tokenize(x["content"], TINY["vocab"])
+        assert len(ids) == NEW and orc.detokenize(ids) == x["content"]
+
+
+def test_cli_single_local_model_passthrough(cli):
+    r = subprocess.run([cli, "--models", "local-tiny", "--judge", "local-tiny", "--max-new-tokens", "5", "--seed", "7",
+                        "--json", "hello"], capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, r.stderr
+    doc = json.loads(r.stdout)
+    want, margin = oracle_answer(7, "hello", 5)
+    assert doc["consensus"] == doc["responses"][0]["content"]  # one response: judge not called (judge.go:74-79)
+    if margin > 1e-3:
+        assert doc["consensus"] == want
+
+
+def test_cli_local_timeout_lands_in_warnings(cli):
+    # a 1 s per-model timeout with far more tokens than fit: the context is polled between decode chunks
+    r = subprocess.run([cli, "--models", "local-tiny-s0", "--judge", "j", "--stub", "j=openai:0:4", "--stub",
+                        "ok=google:1:fine", "--max-new-tokens", "6000", "--timeout", "1", "--json", "hi"],
+                       capture_output=True, text=True, timeout=300)
+    assert r.returncode == 1
+    assert r.stderr == "error: running queries: all models failed: [local-tiny-s0: context deadline exceeded]\n"
