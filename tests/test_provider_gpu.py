@@ -74,9 +74,10 @@ def test_cli_single_local_model_passthrough(cli):
 
 
 def test_cli_local_timeout_lands_in_warnings(cli):
-    # a 1 s per-model timeout with far more tokens than fit: the context is polled between decode chunks
-    r = subprocess.run([cli, "--models", "local-tiny-s0", "--judge", "j", "--stub", "j=openai:0:4", "--stub",
-                        "ok=google:1:fine", "--max-new-tokens", "6000", "--timeout", "1", "--json", "hi"],
+    # a 1 s per-model timeout with several seconds' worth of tokens (1B shape, ~1 ms per token): the context
+    # is polled between decode chunks, so the query is abandoned and reported like any provider error
+    r = subprocess.run([cli, "--models", "local-llama-1b-s0", "--judge", "j", "--stub", "j=openai:0:4",
+                        "--max-new-tokens", "7000", "--timeout", "1", "--json", "hi"],
                        capture_output=True, text=True, timeout=300)
     assert r.returncode == 1
-    assert r.stderr == "error: running queries: all models failed: [local-tiny-s0: context deadline exceeded]\n"
+    assert r.stderr == "error: running queries: all models failed: [local-llama-1b-s0: context deadline exceeded]\n"
