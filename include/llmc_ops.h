@@ -71,6 +71,33 @@ int64_t llmc_debug_tensor(llmc_engine* e, int layer, int kind, uint16_t* out, in
  * position of a slot. */
 int llmc_debug_kv(llmc_engine* e, int slot, int layer, int pos, void* k, void* v);
 
+/* LM head + greedy argmax WITHOUT any device allocation.  No counterpart in the reference (it has no
+ * device code at all); it exists for callers that must not allocate: processes whose GPU memory is
+ * handed out up front by their own arena, plugins inside a framework that owns all allocations, and
+ * latency-critical loops where cudaMalloc/cudaFree (device-wide synchronisation, driver locks) are
+ * banned after start-up.
+ *
+ *   logits[b][n] = sum_k W[n][k] * RMSNorm(x[b]; gain, eps)[k]     (d_logits may be NULL)
+ *   d_tokens[b]  = lowest-index argmax of row b
+ *
+ * Every pointer is a DEVICE pointer the caller already owns (W bf16 bits [V][K], x fp32 [B][K], gain
+ * bf16 bits [K], logits fp32 [B][V], tokens int32 [B]); `stream` is the caller's cudaStream_t (NULL
+ * = default stream).  The call only enqueues work: results are valid once the stream has been
+ * synchronised.  The kernel's scratch (per-block argmax candidates, a block counter) sits in a
+ * 2 MiB + 512 B array inside the library image, which every GPU that loads the library keeps until
+ * exit.  Limits: 1 <= B <= LLMC_NOALLOC_MAX_BATCH, V a multiple of 4 and <= LLMC_NOALLOC_MAX_VOCAB,
+ * K a multiple of 256; anything larger is refused with LLMC_ERR_LIMIT.  The first call on a device
+ * looks the array's device address up and fills a small table in it; make that first call before any
+ * stream capture begins.  All calls share the one array: it is cleared where the kernel needs zeros,
+ * but two calls whose kernels can overlap on one GPU (different streams, different threads) race.
+ * Neither cudaMalloc/cudaFree nor any allocating library routine is called. */
+#define LLMC_NOALLOC_MAX_BATCH 8
+#define LLMC_NOALLOC_MAX_VOCAB 262144
+int llmc_lmhead_argmax_noalloc(int device, int V, int K, int B, const uint16_t* d_W, const float* d_x,
+                               const uint16_t* d_gain, float eps, float* d_logits, int32_t* d_tokens,
+                               void* stream);
+const char* llmc_noalloc_last_error(void);
+
 #ifdef __cplusplus
 }
 #endif

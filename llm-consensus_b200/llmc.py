@@ -25,6 +25,7 @@ ENGINE_SYMBOLS = [
 OPS_SYMBOLS = [
     "llmc_ops_last_error", "llmc_op_gemv", "llmc_op_gemv_swiglu", "llmc_op_lmhead", "llmc_op_attn_decode",
     "llmc_op_gemm", "llmc_op_rmsnorm_rows", "llmc_op_prefill_attention", "llmc_debug_tensor", "llmc_debug_kv",
+    "llmc_lmhead_argmax_noalloc", "llmc_noalloc_last_error",
 ]
 
 
@@ -86,6 +87,8 @@ def lib():
         l.llmc_debug_tensor.argtypes = [vp, C.c_int, C.c_int, vp, C.c_int64]
         l.llmc_debug_tensor.restype = C.c_int64
         l.llmc_debug_kv.argtypes = [vp, C.c_int, C.c_int, C.c_int, vp, vp]
+        l.llmc_lmhead_argmax_noalloc.argtypes = [C.c_int] * 4 + [vp, vp, vp, C.c_float, vp, vp, vp]
+        l.llmc_noalloc_last_error.restype = C.c_char_p
         _lib = l
     return _lib
 
