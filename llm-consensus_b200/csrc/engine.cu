@@ -18,6 +18,7 @@
 //             attn[T][nq d], act[T][I] as bf16 hi (+ lo) pairs, for T = prefill_chunk
 #include <cuda_runtime.h>
 #include <math.h>
+#include <stdlib.h>
 #include <string.h>
 #include <algorithm>
 #include <map>
@@ -335,6 +336,7 @@ static int create_impl(llmc_engine* e, const llmc_config& c) {
   e->kv_fp32 = (c.flags & LLMC_FLAG_KV_BF16) ? 0 : 1;
   e->kv_elem = e->kv_fp32 ? 4 : 2;
   e->split_prefill = !(c.flags & LLMC_FLAG_PREFILL_BF16);
+  e->use_mega = !(c.flags & LLMC_FLAG_NO_MEGAKERNEL);
   e->stats.sm_count = e->prop.multiProcessorCount; e->stats.cc_major = e->prop.major; e->stats.cc_minor = e->prop.minor;
   E_TRY(cudaStreamCreateWithFlags(&e->stream, cudaStreamNonBlocking));
   E_TRY(cudaEventCreate(&e->ev0));
@@ -397,6 +399,27 @@ static int create_impl(llmc_engine* e, const llmc_config& c) {
   E_TRY(cudaMemsetAsync(e->attn_counters, 0, (size_t)MB * d.kv_heads * sizeof(unsigned), e->stream));
   E_TRY(cudaMemsetAsync(e->d_step_counter, 0, sizeof(int), e->stream));
   E_TRY(cudaMemsetAsync(e->d_dummy_counter, 0, sizeof(int), e->stream));
+  // ---- one-kernel batch-1 decode
+  {
+    std::vector<MegaLayer> ml(d.layers);
+    for (int l = 0; l < d.layers; ++l) {
+      const LayerW& w = e->L[l];
+      ml[l] = MegaLayer{w.wqkv, w.wo, w.wgu, w.wd, w.g1, w.g2,
+                        e->kpool + (size_t)l * e->kv_layer_stride * e->kv_elem,
+                        e->vpool + (size_t)l * e->kv_layer_stride * e->kv_elem};
+    }
+    if (int rc = dalloc(e, &e->d_mega_layers, (size_t)d.layers)) return rc;
+    E_TRY(cudaMemcpy(e->d_mega_layers, ml.data(), ml.size() * sizeof(MegaLayer), cudaMemcpyHostToDevice));
+    e->mega_max_tiles = std::max(8, (e->max_ctx + 31) / 32);
+    if (int rc = dalloc(e, &e->mega_scratch, (size_t)d.q_heads * e->mega_max_tiles * (D + 2))) return rc;
+    if (int rc = dalloc(e, &e->mega_part_val, (size_t)e->prop.multiProcessorCount)) return rc;
+    if (int rc = dalloc(e, &e->mega_part_idx, (size_t)e->prop.multiProcessorCount)) return rc;
+    if (int rc = dalloc(e, &e->mega_barrier, 1)) return rc;
+    if (int rc = dalloc(e, &e->mega_counters, (size_t)d.kv_heads)) return rc;
+    if (getenv("LLMC_MEGA_TRACE"))
+      if (int rc = dalloc(e, &e->mega_trace, (size_t)2 * (5 * d.layers + 1) * 64)) return rc;
+    E_TRY(cudaMemsetAsync(e->mega_counters, 0, (size_t)d.kv_heads * sizeof(unsigned), e->stream));
+  }
   // ---- prefill workspace
   const int TC = e->prefill_chunk;
   if (int rc = dalloc(e, &e->p_tokens, TC)) return rc;
@@ -599,12 +622,31 @@ int llmc_decode(llmc_engine* e, const int32_t* slots, int32_t nslots, int32_t ns
   // context it will reach (the graph is keyed by it)
   const int nsplit = attn_decode_nsplit(max_len + nsteps);
   cudaGraphExec_t ge = nullptr;
-  if (e->use_graph) {
+  if (e->use_graph && !(e->use_mega && nslots == 1)) {
     int rc = get_graph(e, nslots, want_logits, nsplit, &ge);
     if (rc != LLMC_OK) return rc;
   }
+  const bool mega = e->use_mega && nslots == 1;
+  if (mega) ge = nullptr;
   E_TRY(cudaEventRecord(e->ev0, s));
-  for (int st = 0; st < nsteps; ++st) {
+  if (mega) {
+    MegaArgs m;
+    memset(&m, 0, sizeof(m));
+    m.layers = e->d_mega_layers; m.L = d.layers; m.H = d.hidden; m.QD = d.qd(); m.KD = d.kd(); m.I = d.inter;
+    m.V = d.vocab; m.q_heads = d.q_heads; m.kv_heads = d.kv_heads; m.head_dim = d.head_dim; m.eps = d.rms_eps;
+    m.emb = e->emb; m.lmhead = e->lmhead; m.gf = e->gf; m.rope_cos = e->rope_cos; m.rope_sin = e->rope_sin;
+    m.block_table = e->d_block_table; m.slot = slots[0]; m.bt_stride = e->pages_per_seq; m.page_size = e->page_size;
+    m.kv_fp32 = e->kv_fp32; m.seq_len = e->d_seq_len; m.next_token = e->d_next_token;
+    m.x = e->x; m.q = e->q; m.attn = e->attn; m.act = e->act; m.logits = want_logits ? e->logits : nullptr;
+    m.attn_scratch = e->mega_scratch; m.max_tiles = e->mega_max_tiles; m.attn_counters = e->mega_counters;
+    m.part_val = e->mega_part_val; m.part_idx = e->mega_part_idx; m.out_tokens = e->d_out_tokens; m.nsteps = nsteps;
+    m.barrier = e->mega_barrier;
+    m.trace = (e->mega_trace && nsteps <= 64) ? e->mega_trace : nullptr;
+    E_TRY(cudaMemsetAsync(e->mega_barrier, 0, sizeof(unsigned), s));
+    E_TRY(launch_decode_mega(m, e->prop.multiProcessorCount, s));
+    e->stats.kernel_launches += 1;
+  }
+  for (int st = 0; st < nsteps && !mega; ++st) {
     if (ge) {
       E_TRY(cudaGraphLaunch(ge, s));
       e->stats.kernel_launches += (uint64_t)d.layers * 5 + 1;
@@ -621,6 +663,25 @@ int llmc_decode(llmc_engine* e, const int32_t* slots, int32_t nslots, int32_t ns
     E_TRY(cudaMemcpyAsync(logits, e->logits, (size_t)nslots * d.vocab * sizeof(float), cudaMemcpyDeviceToHost, s));
   E_TRY(cudaStreamSynchronize(s));
   E_TRY(cudaGetLastError());
+  if (mega && e->mega_trace && nsteps <= 64) {
+    // debug trace: average per-phase time (barrier open -> next barrier open) and barrier wait of block 0
+    const int nb = (5 * d.layers + 1) * nsteps;
+    std::vector<unsigned long long> t((size_t)2 * nb);
+    E_TRY(cudaMemcpy(t.data(), e->mega_trace, t.size() * sizeof(unsigned long long), cudaMemcpyDeviceToHost));
+    const char* names[6] = {"qkv", "attn", "o", "gateup", "down", "lmhead"};
+    double phase[6] = {0, 0, 0, 0, 0, 0}, wait[6] = {0, 0, 0, 0, 0, 0};
+    int cnt[6] = {0, 0, 0, 0, 0, 0};
+    const int per = 5 * d.layers + 1;
+    for (int i = 1; i < nb; ++i) {
+      const int k = (i % per) == per - 1 ? 5 : (i % per) % 5;
+      phase[k] += (double)(t[2 * i + 1] - t[2 * (i - 1) + 1]);
+      wait[k] += (double)(t[2 * i + 1] - t[2 * i]);
+      cnt[k]++;
+    }
+    for (int k = 0; k < 6; ++k)
+      if (cnt[k]) fprintf(stderr, "[mega trace] %-7s phase %.2f us (block 0 waited %.2f us at its barrier) x%d\n", names[k],
+                          phase[k] / cnt[k] / 1e3, wait[k] / cnt[k] / 1e3, cnt[k]);
+  }
   if (out_tokens) memcpy(out_tokens, host.data(), host.size() * sizeof(int));
   for (int i = 0; i < nslots; ++i) e->h_seq_len[slots[i]] += nsteps;
   e->stats.decode_steps += nsteps;

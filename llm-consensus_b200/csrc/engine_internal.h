@@ -57,6 +57,15 @@ struct llmc_engine {
   float *px = nullptr, *pqkv = nullptr, *pq = nullptr;
   uint16_t *pxn = nullptr, *pattn = nullptr, *pact = nullptr;
   uint16_t *pxn_lo = nullptr, *pattn_lo = nullptr, *pact_lo = nullptr;  // split-bf16 low halves (or NULL)
+  // one-kernel batch-1 decode
+  bool use_mega = true;
+  llmc::MegaLayer* d_mega_layers = nullptr;
+  float* mega_scratch = nullptr;
+  int mega_max_tiles = 0;
+  float* mega_part_val = nullptr;
+  int* mega_part_idx = nullptr;
+  unsigned *mega_barrier = nullptr, *mega_counters = nullptr;
+  unsigned long long* mega_trace = nullptr;  // LLMC_MEGA_TRACE=1: per-barrier times of the last launch
   std::map<int, cudaGraphExec_t> graphs;  // key = (B * 2 + want_logits) * 16 + nsplit
   std::mutex mu;
   std::string last_error;

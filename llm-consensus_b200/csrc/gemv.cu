@@ -183,7 +183,9 @@ __global__ void __launch_bounds__(GemvCfg<EPI>::WARPS * 32) gemv_kernel(const Ge
 #pragma unroll
     for (int b = 0; b < BT; ++b) acc[r][b] = 0.f;
 
-  for (int it0 = it_lo; it0 < it_hi; it0 += UK) {
+  // ping-pong: the batch just consumed is re-requested at once and left alone until the other batch
+  // has been consumed (copying wnxt into wcur would stall on the loads still in flight)
+  auto consume = [&](uint4(&w)[R][UK], int it0) {
 #pragma unroll
     for (int u = 0; u < UK; ++u) {
       const int it = it0 + u;
@@ -194,15 +196,15 @@ __global__ void __launch_bounds__(GemvCfg<EPI>::WARPS * 32) gemv_kernel(const Ge
           const float4 x0 = *reinterpret_cast<const float4*>(xp + (size_t)b * K);
           const float4 x1 = *reinterpret_cast<const float4*>(xp + (size_t)b * K + 128);
 #pragma unroll
-          for (int r = 0; r < R; ++r) acc[r][b] += dot8(wcur[r][u], x0, x1);
+          for (int r = 0; r < R; ++r) acc[r][b] += dot8(w[r][u], x0, x1);
         }
       }
     }
-#pragma unroll
-    for (int u = 0; u < UK; ++u)
-#pragma unroll
-      for (int r = 0; r < R; ++r) wcur[r][u] = wnxt[r][u];
-    load_batch(wnxt, it0 + 2 * UK);
+    if (it0 + 2 * UK < it_hi) load_batch(w, it0 + 2 * UK);
+  };
+  for (int it0 = it_lo; it0 < it_hi; it0 += 2 * UK) {
+    consume(wcur, it0);
+    if (it0 + UK < it_hi) consume(wnxt, it0 + UK);
   }
 #pragma unroll
   for (int r = 0; r < R; ++r)

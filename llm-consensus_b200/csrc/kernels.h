@@ -83,6 +83,36 @@ constexpr int ATTN_MAX_SPLIT = 8;
 // blocks per (sequence, kv head) for a batch whose longest context is max_ctx_tokens
 int attn_decode_nsplit(int max_ctx_tokens);
 
+// ------------------------------------------------------------------ decode_mega.cu (batch-1 decode, one kernel)
+struct MegaLayer {
+  const uint16_t *wqkv, *wo, *wgu, *wd, *g1, *g2;
+  void *kp, *vp;  // this layer's K / V pages
+};
+struct MegaArgs {
+  const MegaLayer* layers;  // device array [L]
+  int L, H, QD, KD, I, V, q_heads, kv_heads, head_dim;
+  float eps;
+  const uint16_t *emb, *lmhead, *gf;
+  const float *rope_cos, *rope_sin;
+  const int* block_table;
+  int slot, bt_stride, page_size, kv_fp32;
+  int* seq_len;       // [max_slots]: read at start, written at the end
+  int* next_token;    // [max_slots]
+  float *x, *q, *attn, *act;   // batch-1 work vectors
+  float* logits;      // nullable: logits of the LAST step
+  float* attn_scratch;         // [kv_heads][max_tiles][G][head_dim + 2]
+  int max_tiles;
+  unsigned* attn_counters;     // [kv_heads], zero on entry, left zero
+  float* part_val;             // [grid]
+  int* part_idx;
+  int* out_tokens;             // [nsteps]
+  int nsteps;
+  unsigned* barrier;           // zero on entry
+  unsigned long long* trace;   // nullable: per-barrier (arrive, open) times of block 0, ns
+  int smem_x;                  // filled by the launcher
+};
+cudaError_t launch_decode_mega(const MegaArgs& a, int sm_count, cudaStream_t s);
+
 // ------------------------------------------------------------------ prefill.cu
 cudaError_t launch_embed_rows(const uint16_t* emb, const int* tokens, int T, int H, float* x, cudaStream_t s);
 // RMSNorm of fp32 rows -> bf16 GEMM operand.  out_lo != NULL: split form, x = hi + lo with both bf16

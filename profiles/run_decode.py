@@ -14,6 +14,7 @@ eng = llmc.Engine(shape=shape, seed=0, max_ctx=1024, max_slots=2, flags=flags)
 prompt = np.random.default_rng(1).integers(0, 128256, 512)
 slot = eng.seq_alloc()
 eng.prefill(slot, prompt)
+eng.decode([slot], 2)          # warm-up: module load, graph capture, first cooperative launch
 eng.decode([slot], steps)
 st = eng.stats()
 print("prefill_ms", st["last_prefill_ms"], "decode_ms_per_step", st["last_decode_ms"] / steps, "launches", st["kernel_launches"])

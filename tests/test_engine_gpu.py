@@ -83,7 +83,7 @@ def test_prefill_logits_and_kv(gpu, name, n_prompt, impl, request):
     e.close()
 
 
-@pytest.mark.parametrize("flags", [0, 3, 1, 2])
+@pytest.mark.parametrize("flags", [0, 16, 19, 17, 18, 4, 20])   # 0: one-kernel decode; 16: 81 kernels per step (+1 no graph, +2 no PDL); 4: bf16 KV
 @pytest.mark.parametrize("name", ["tiny", "tiny-untied", "small-d128"])
 def test_teacher_forced_decode_logits(gpu, name, flags):
     """Every decode step's logits against the oracle, both fed the ORACLE's greedy tokens."""
@@ -104,6 +104,9 @@ def test_teacher_forced_decode_logits(gpu, name, flags):
         agree += int(out[0, 0] == otoks[s])
     assert worst <= TOL, "decode logits max-abs %.3e" % worst
     assert e.seq_len(slot) == len(prompt) + n_new - 1
+    # several steps in one call continue from the same device-resident state
+    more = e.decode([slot], 5)
+    assert more.shape == (1, 5) and e.seq_len(slot) == len(prompt) + n_new + 4
     print("teacher-forced argmax agreement %d/%d, worst logit err %.2e" % (agree, n_new, worst))
     e.close()
 
@@ -118,9 +121,9 @@ def greedy_agreement(otoks, olog, gtoks, tol=TOL):
 
 
 @pytest.mark.parametrize("name", ["tiny", "tiny-untied", "small-d128"])
-@pytest.mark.parametrize("chunk", [1, 7, 64])
-def test_free_running_greedy_tokens(gpu, name, chunk):
-    o, e = make_pair(gpu, name, seed=13)
+@pytest.mark.parametrize("chunk,flags", [(1, 0), (7, 0), (64, 0), (7, 16), (64, 16)])
+def test_free_running_greedy_tokens(gpu, name, chunk, flags):
+    o, e = make_pair(gpu, name, seed=13, flags=flags)
     V = DIMS[name]["vocab"]
     prompt = np.random.default_rng(9).integers(0, V, 33)
     n_new = 64
