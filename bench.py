@@ -73,7 +73,7 @@ class ClockSampler(threading.Thread):
                 "samples": len(self.rows)}
 
 
-def cpu_sample(threads_all=True, prompt_len=64, new_tokens=32, steps=1, warmup=0):
+def cpu_sample(threads_all=True, prompt_len=128, new_tokens=64, steps=3, warmup=0):
     """The fp32 CPU oracle on a bounded sample of the workload (same shape, same prompt/decode ratio)."""
     from oracle import ref
     o = ref.Oracle("llama-1b", seed=0, max_ctx=prompt_len + new_tokens + 8)
@@ -88,19 +88,19 @@ def cpu_sample(threads_all=True, prompt_len=64, new_tokens=32, steps=1, warmup=0
     dt = sum(times)
     return {"value": new_tokens * len(times) / dt, "unit": "tok/s", "cores": ref.num_threads(), "kind": "port",
             "sample": "fp32 C++/OpenMP oracle (oracle/llama_ref.cpp), Llama-3.2-1B shape, %d-token prompt + %d greedy "
-                      "tokens per step (the 512+256 workload scaled 1/8, same 2:1 ratio), %d step(s), %.1f s"
+                      "tokens per step (the 512+256 workload scaled down, same 2:1 ratio), %d step(s), %.1f s"
                       % (prompt_len, new_tokens, len(times), dt)}, dt / len(times)
 
 
 def run_reference(args, rank, world):
     if rank != 0:
         return
-    base, ms = cpu_sample(steps=args.steps, warmup=min(args.warmup, 1))
+    base, ms = cpu_sample(steps=max(1, min(args.steps, 8)), warmup=min(args.warmup, 1))
     line = {"impl": "reference", "metric": METRIC, "value": base["value"], "unit": "tok/s", "n_gpus": args.gpus,
             "steps": args.steps, "warmup": min(args.warmup, 1), "ms_per_step": ms * 1e3, "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "config": {"workload": "local provider query, Llama-3.2-1B shape random-init, 512-token prompt + 256 greedy "
-                                   "tokens (BASELINE.json configs[1]); CPU arm runs a 1/8 sample per step",
+                                   "tokens (BASELINE.json configs[1]); CPU arm runs a 1/4-scale sample (128 + 64 tokens) per step",
                        "shape": "llama-3.2-1b", "prompt": PROMPT_LEN, "new_tokens": NEW_TOKENS, "batch": 1},
             "cpu_baseline": base,
             "e2e": {"value": base["value"], "unit": "tok/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
@@ -191,6 +191,10 @@ def run_ours(args, rank, world, local_rank):
     step_s = dec_ms / 1e3 / steps_dec
     peak, peak_src = peaks()
     achieved = bytes_per_step / step_s / 1e9
+    traffic = None
+    tp = os.path.join(ROOT, "profiles", "r1_mega_traffic.json")
+    if os.path.exists(tp):
+        traffic = json.load(open(tp))["dram_bytes_per_step"]
     line = {
         "metric": METRIC, "value": value, "unit": "tok/s", "n_gpus": world, "steps": args.steps,
         "warmup": max(args.warmup, 3), "ms_per_step": dev_ms / args.steps, "higher_is_better": True,
@@ -200,7 +204,8 @@ def run_ours(args, rank, world, local_rank):
                                "no collective",
                    "shape": "llama-3.2-1b", "prompt": PROMPT_LEN, "new_tokens": NEW_TOKENS, "batch": 1,
                    "l2": "no flush needed: each decode step streams 2.47 GB of weights, 20x the 126 MB L2",
-                   "graph": st["graph_enabled"], "pdl": st["pdl_enabled"]},
+                   "decode_path": "persistent cooperative kernel (batch 1)", "kv_cache": "fp32",
+                   "prefill_operands": "bf16 hi+lo pairs"},
         "decode_only_tok_s_per_gpu": steps_dec / (dec_ms / 1e3),
         "prefill_ms": pre_ms / args.steps,
         "queries_per_s": args.steps * world / (dev_ms / 1e3),
@@ -210,8 +215,10 @@ def run_ours(args, rank, world, local_rank):
                         "(H2D of the prompt ids and D2H of the generated ids every step)"},
         "gpu_launches": int(launches_all),
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                     "traffic": None, "peak_source": peak_src, "frac_of_8TBs_nominal": achieved / 8000.0,
-                     "kernel": "one decode step = one CUDA-graph launch of 5 kernels/layer x 16 + LM head",
+                     "traffic": traffic, "peak_source": peak_src, "frac_of_8TBs_nominal": achieved / 8000.0,
+                     "kernel": "decode_mega_kernel: one persistent cooperative kernel runs every decode step of a "
+                               "llmc_decode call (5 phases/layer x 16 + LM head per step); figures are per step",
+                     "traffic_source": "profiles/r1_mega_traffic.json (ncu --set full, dram__bytes_read.sum / steps)",
                      "algorithmic_bytes_per_launch": bytes_per_step, "avg_launch_us": step_s * 1e6},
         "clocks": clocks,
     }
