@@ -75,6 +75,8 @@ class ClockSampler(threading.Thread):
 
 def cpu_sample(threads_all=True, prompt_len=128, new_tokens=64, steps=3, warmup=0):
     """The fp32 CPU oracle on a bounded sample of the workload (same shape, same prompt/decode ratio)."""
+    # torchrun exports OMP_NUM_THREADS=1 to every rank; the CPU legs are meant to use all host threads
+    os.environ["OMP_NUM_THREADS"] = str(os.cpu_count() or 1)
     from oracle import ref
     o = ref.Oracle("llama-1b", seed=0, max_ctx=prompt_len + new_tokens + 8)
     prompt = np.random.default_rng(1).integers(0, 128256, prompt_len)

@@ -251,6 +251,27 @@ def test_error_paths(gpu):
     e.close()
 
 
+def test_llama8b_shape_short(gpu):
+    """The 8B shape (head_dim 128, K 4096 / 14336, untied LM head) at full width on a short sequence:
+    teacher-forced logits against the oracle, through both decode paths."""
+    o = ref.Oracle("llama-8b", seed=2, max_ctx=64)
+    prompt = np.random.default_rng(3).integers(0, 128256, 40)
+    n_new = 4
+    otoks, olog = o.generate(prompt, n_new, want_logits=True)
+    for flags in (0, 16):
+        e = gpu.Engine(shape=gpu.SHAPE_LLAMA_8B, seed=2, max_ctx=64, max_slots=1, prefill_impl=DEFAULT_IMPL, flags=flags)
+        slot = e.seq_alloc()
+        nxt, lg = e.prefill(slot, prompt, want_logits=True)
+        worst = float(np.abs(lg - olog[0]).max())
+        for s in range(1, n_new):
+            e.set_next_token(slot, otoks[s - 1])
+            out, lg = e.decode([slot], 1, want_logits=True)
+            worst = max(worst, float(np.abs(lg[0] - olog[s]).max()))
+        print("8B shape flags %d: worst logit err %.2e (logit std %.3f)" % (flags, worst, float(olog.std())))
+        assert worst <= TOL
+        e.close()
+
+
 def test_config2_llama1b_512_prompt_256_decode(gpu):
     """BASELINE.json configs[1] at full size: Llama-3.2-1B shape, seed 0, 512-token prompt, 256 greedy
     tokens; logits teacher-forced on the oracle's tokens, every step, max-abs <= 2e-2; argmax
