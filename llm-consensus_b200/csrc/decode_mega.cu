@@ -120,11 +120,13 @@ __device__ __forceinline__ void grid_barrier(unsigned* bar, unsigned& target, un
   __syncthreads();
   if (threadIdx.x == 0) {
     if (trace && blockIdx.x == 0) trace[2 * tix] = gtime();
-    __threadfence();
-    atomicAdd(bar, 1u);
-    while (*reinterpret_cast<volatile unsigned*>(bar) < target) {
-    }
-    __threadfence();
+    // release-add / acquire-poll at gpu scope: the block's writes (ordered before this thread by the
+    // barrier above) become visible to every block that observes the count, without a full membar
+    asm volatile("red.release.gpu.global.add.u32 [%0], 1;" ::"l"(bar) : "memory");
+    unsigned v;
+    do {
+      asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(bar) : "memory");
+    } while (v < target);
     if (trace && blockIdx.x == 0) trace[2 * tix + 1] = gtime();
   }
   __syncthreads();
