@@ -594,20 +594,9 @@ int llmc_prefill(llmc_engine* e, int32_t slot, const int32_t* tokens, int32_t n,
   return LLMC_OK;
 }
 
-int llmc_decode(llmc_engine* e, const int32_t* slots, int32_t nslots, int32_t nsteps, int32_t* out_tokens,
-                float* logits) {
-  if (!e || !slots) return e ? fail(e, LLMC_ERR_INVALID, "llmc_decode: null slots") : LLMC_ERR_INVALID;
-  std::lock_guard<std::mutex> lk(e->mu);
-  if (nslots < 1 || nslots > MAX_GEMV_BATCH)
-    return fail(e, LLMC_ERR_LIMIT, "llmc_decode: nslots must be in [1," + std::to_string(MAX_GEMV_BATCH) + "]");
-  if (nsteps < 1 || nsteps > MAX_STEPS_PER_CALL)
-    return fail(e, LLMC_ERR_LIMIT, "llmc_decode: nsteps must be in [1," + std::to_string(MAX_STEPS_PER_CALL) + "]");
-  for (int i = 0; i < nslots; ++i) {
-    if (int rc = check_slot(e, slots[i])) return rc;
-    if (e->h_seq_len[slots[i]] < 1) return fail(e, LLMC_ERR_STATE, "llmc_decode: slot has no prefilled tokens");
-    for (int j = 0; j < i; ++j)
-      if (slots[j] == slots[i]) return fail(e, LLMC_ERR_INVALID, "llmc_decode: duplicate slot");
-  }
+// one group of <= MAX_GEMV_BATCH sequences decoded together (engine mutex held by the caller)
+static int decode_group(llmc_engine* e, const int32_t* slots, int32_t nslots, int32_t nsteps, int32_t* out_tokens,
+                        float* logits) {
   E_TRY(cudaSetDevice(e->device));
   for (int i = 0; i < nslots; ++i)
     if (int rc = ensure_pages(e, slots[i], e->h_seq_len[slots[i]] + nsteps)) return rc;
@@ -684,8 +673,39 @@ int llmc_decode(llmc_engine* e, const int32_t* slots, int32_t nslots, int32_t ns
   }
   if (out_tokens) memcpy(out_tokens, host.data(), host.size() * sizeof(int));
   for (int i = 0; i < nslots; ++i) e->h_seq_len[slots[i]] += nsteps;
-  e->stats.decode_steps += nsteps;
   cudaEventElapsedTime(&e->stats.last_decode_ms, e->ev0, e->ev1);
+  return LLMC_OK;
+}
+
+int llmc_decode(llmc_engine* e, const int32_t* slots, int32_t nslots, int32_t nsteps, int32_t* out_tokens,
+                float* logits) {
+  if (!e || !slots) return e ? fail(e, LLMC_ERR_INVALID, "llmc_decode: null slots") : LLMC_ERR_INVALID;
+  std::lock_guard<std::mutex> lk(e->mu);
+  if (nslots < 1 || nslots > e->max_slots)
+    return fail(e, LLMC_ERR_LIMIT, "llmc_decode: nslots must be in [1," + std::to_string(e->max_slots) + "]");
+  if (nsteps < 1 || nsteps > MAX_STEPS_PER_CALL)
+    return fail(e, LLMC_ERR_LIMIT, "llmc_decode: nsteps must be in [1," + std::to_string(MAX_STEPS_PER_CALL) + "]");
+  for (int i = 0; i < nslots; ++i) {
+    if (int rc = check_slot(e, slots[i])) return rc;
+    if (e->h_seq_len[slots[i]] < 1) return fail(e, LLMC_ERR_STATE, "llmc_decode: slot has no prefilled tokens");
+    for (int j = 0; j < i; ++j)
+      if (slots[j] == slots[i]) return fail(e, LLMC_ERR_INVALID, "llmc_decode: duplicate slot");
+    if (e->h_seq_len[slots[i]] + nsteps > e->max_ctx)
+      return fail(e, LLMC_ERR_LIMIT, "sequence would exceed max_ctx (" + std::to_string(e->max_ctx) + " tokens)");
+  }
+  // The decode kernels batch up to 8 sequences against one pass over the weights; larger batches are
+  // run as consecutive groups of 8 (sequences are independent, so the order does not matter).  A
+  // tensor-core skinny GEMM that keeps batches of 16-128 on the HBM roof is future work.
+  float total_ms = 0.f;
+  for (int g0 = 0; g0 < nslots; g0 += MAX_GEMV_BATCH) {
+    const int n = std::min<int>(MAX_GEMV_BATCH, nslots - g0);
+    int rc = decode_group(e, slots + g0, n, nsteps, out_tokens ? out_tokens + (size_t)g0 * nsteps : nullptr,
+                          logits ? logits + (size_t)g0 * e->d.vocab : nullptr);
+    if (rc != LLMC_OK) return rc;
+    total_ms += e->stats.last_decode_ms;
+  }
+  e->stats.last_decode_ms = total_ms;
+  e->stats.decode_steps += nsteps;
   return LLMC_OK;
 }
 

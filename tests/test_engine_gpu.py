@@ -185,11 +185,11 @@ def test_chunked_prefill_equals_single_pass(gpu):
     e.close(); e2.close()
 
 
-@pytest.mark.parametrize("B", [2, 3, 5, 8])
+@pytest.mark.parametrize("B", [2, 3, 5, 8, 11])
 def test_batched_decode_matches_per_sequence_oracle(gpu, B):
     name = "tiny"
     V = DIMS[name]["vocab"]
-    e = gpu.Engine(dims=DIMS[name], seed=4, max_ctx=256, max_slots=8, prefill_impl=DEFAULT_IMPL)
+    e = gpu.Engine(dims=DIMS[name], seed=4, max_ctx=256, max_slots=12, prefill_impl=DEFAULT_IMPL)
     rng = np.random.default_rng(B)
     prompts = [rng.integers(0, V, int(n)) for n in rng.integers(3, 90, B)]
     slots, firsts = [], []
