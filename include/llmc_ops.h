@@ -50,6 +50,10 @@ int llmc_op_attn_decode(int device, int B, int q_heads, int kv_heads, int head_d
 int llmc_op_gemm(int device, int impl, int epi, int T, int N, int K, const uint16_t* A, const uint16_t* A_lo,
                  const uint16_t* W, void* out, void* out_lo);
 
+/* Times the prefill GEMM on device-resident operands (CUDA events around `iters` launches, 3 warm-up
+ * launches first); split != 0 uses the hi+lo A operand.  For the tensor-pipe utilisation figures. */
+int llmc_op_gemm_bench(int device, int impl, int epi, int split, int T, int N, int K, int iters, float* ms_per_call);
+
 /* Row-wise RMSNorm fp32 -> bf16 (hi, and lo if out_lo != NULL: x = hi + lo). */
 int llmc_op_rmsnorm_rows(int device, int T, int H, const float* x, const uint16_t* gain, float eps, uint16_t* out,
                          uint16_t* out_lo);

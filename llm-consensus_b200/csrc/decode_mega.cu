@@ -309,7 +309,7 @@ __global__ void __launch_bounds__(MW * 32, 1) decode_mega_kernel(const MegaArgs 
       // 32-position tile each (tiles split, split + nsp, ...), their softmax states meet in shared memory and
       // one record per (kv head, split, q head) goes to the scratch.  nsp is chosen so that a block has
       // about 4 tiles: the work spreads over tens of SMs, and the cross-block merge (P3) has few terms.
-      const int nsp = min(MEGA_MAX_SPLIT, max(1, (ntiles + 3) / 4));
+      const int nsp = min(MEGA_MAX_SPLIT, max(1, (ntiles + a.attn_tiles_per_block - 1) / a.attn_tiles_per_block));
       {
         float* qs = xs;                                            // [G][D]
         float* part = xs + G * D;                                  // [MW][G][PS]

@@ -630,6 +630,10 @@ static int decode_group(llmc_engine* e, const int32_t* slots, int32_t nslots, in
     m.attn_scratch = e->mega_scratch; m.max_tiles = e->mega_max_tiles; m.attn_counters = e->mega_counters;
     m.part_val = e->mega_part_val; m.part_idx = e->mega_part_idx; m.out_tokens = e->d_out_tokens; m.nsteps = nsteps;
     m.barrier = e->mega_barrier;
+    {
+      const char* tpb = getenv("LLMC_MEGA_TILES_PER_BLOCK");
+      m.attn_tiles_per_block = tpb ? std::max(1, atoi(tpb)) : 4;
+    }
     m.trace = (e->mega_trace && nsteps <= 64) ? e->mega_trace : nullptr;
     E_TRY(cudaMemsetAsync(e->mega_barrier, 0, sizeof(unsigned), s));
     E_TRY(launch_decode_mega(m, e->prop.multiProcessorCount, s));

@@ -109,6 +109,7 @@ struct MegaArgs {
   int nsteps;
   unsigned* barrier;           // zero on entry
   unsigned long long* trace;   // nullable: per-barrier (arrive, open) times of block 0, ns
+  int attn_tiles_per_block;    // attention: tiles per (kv head, split) block; splits = ceil(tiles / this), <= 8
   int smem_x;                  // filled by the launcher
 };
 cudaError_t launch_decode_mega(const MegaArgs& a, int sm_count, cudaStream_t s);

@@ -267,6 +267,43 @@ int llmc_op_gemm(int device, int impl, int epi, int T, int N, int K, const uint1
   return LLMC_OK;
 }
 
+int llmc_op_gemm_bench(int device, int impl, int epi, int split, int T, int N, int K, int iters, float* ms_per_call) {
+  if (T < 1 || iters < 1 || !ms_per_call) return ofail(LLMC_ERR_INVALID, "llmc_op_gemm_bench: bad argument");
+  O_TRY(cudaSetDevice(device));
+  Pool pool;
+  uint16_t *dA, *dAl = nullptr, *dW;
+  unsigned char *dout, *dol = nullptr;
+  const size_t out_cols = epi == GEMM_SWIGLU_BF16 ? N / 2 : N;
+  const size_t out_bytes = (size_t)T * out_cols * 4;
+  O_TRY(pool.get(&dA, (size_t)T * K));
+  if (split) O_TRY(pool.get(&dAl, (size_t)T * K));
+  O_TRY(pool.get(&dW, (size_t)N * K));
+  O_TRY(pool.get(&dout, out_bytes));
+  if (split && epi == GEMM_SWIGLU_BF16) O_TRY(pool.get(&dol, out_bytes));
+  // operands: a fixed non-trivial bit pattern (bf16 0x3c00.. small values); timing only
+  O_TRY(cudaMemset(dA, 0x3c, (size_t)T * K * 2));
+  O_TRY(cudaMemset(dW, 0x3c, (size_t)N * K * 2));
+  cudaEvent_t e0, e1;
+  O_TRY(cudaEventCreate(&e0));
+  O_TRY(cudaEventCreate(&e1));
+  auto run = [&]() {
+    return impl == 0 ? launch_gemm_tcgen05(dA, dAl, dW, dout, dol, T, N, K, epi, 0)
+                     : launch_gemm_simple(dA, dAl, dW, dout, dol, T, N, K, epi, 0);
+  };
+  for (int i = 0; i < 3; ++i) O_TRY(run());
+  O_TRY(cudaDeviceSynchronize());
+  O_TRY(cudaEventRecord(e0, 0));
+  for (int i = 0; i < iters; ++i) O_TRY(run());
+  O_TRY(cudaEventRecord(e1, 0));
+  O_TRY(cudaDeviceSynchronize());
+  float ms = 0.f;
+  cudaEventElapsedTime(&ms, e0, e1);
+  cudaEventDestroy(e0);
+  cudaEventDestroy(e1);
+  *ms_per_call = ms / iters;
+  return LLMC_OK;
+}
+
 int llmc_op_rmsnorm_rows(int device, int T, int H, const float* x, const uint16_t* gain, float eps, uint16_t* out,
                          uint16_t* out_lo) {
   if (!x || !gain || !out || T < 1 || H % 8) return ofail(LLMC_ERR_INVALID, "llmc_op_rmsnorm_rows: bad argument");

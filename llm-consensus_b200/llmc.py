@@ -24,7 +24,7 @@ ENGINE_SYMBOLS = [
 ]
 OPS_SYMBOLS = [
     "llmc_ops_last_error", "llmc_op_gemv", "llmc_op_gemv_swiglu", "llmc_op_lmhead", "llmc_op_attn_decode",
-    "llmc_op_gemm", "llmc_op_rmsnorm_rows", "llmc_op_prefill_attention", "llmc_debug_tensor", "llmc_debug_kv",
+    "llmc_op_gemm", "llmc_op_gemm_bench", "llmc_op_rmsnorm_rows", "llmc_op_prefill_attention", "llmc_debug_tensor", "llmc_debug_kv",
     "llmc_lmhead_argmax_noalloc", "llmc_noalloc_last_error",
 ]
 
@@ -82,6 +82,7 @@ def lib():
         l.llmc_op_lmhead.argtypes = [C.c_int] * 4 + [vp, vp, vp, C.c_float, vp, vp]
         l.llmc_op_attn_decode.argtypes = [C.c_int] * 9 + [vp] * 5
         l.llmc_op_gemm.argtypes = [C.c_int] * 6 + [vp] * 5
+        l.llmc_op_gemm_bench.argtypes = [C.c_int] * 8 + [vp]
         l.llmc_op_rmsnorm_rows.argtypes = [C.c_int] * 3 + [vp, vp, C.c_float, vp, vp]
         l.llmc_op_prefill_attention.argtypes = [C.c_int] * 7 + [C.c_float, C.c_int] + [vp] * 8
         l.llmc_debug_tensor.argtypes = [vp, C.c_int, C.c_int, vp, C.c_int64]
@@ -287,6 +288,12 @@ def op_gemm(A, W, epi=1, impl=0, out_in=None, A_lo=None, want_lo=False, device=0
     _ops_check(lib().llmc_op_gemm(device, impl, epi, T, N, K, A.ctypes.data, _ptr(Al), W.ctypes.data, out.ctypes.data,
                                   _ptr(lo)))
     return (out, lo) if want_lo else out
+
+
+def op_gemm_bench(T, N, K, epi=1, split=0, impl=0, iters=20, device=0):
+    ms = C.c_float(0)
+    _ops_check(lib().llmc_op_gemm_bench(device, impl, epi, split, T, N, K, iters, C.byref(ms)))
+    return ms.value
 
 
 def op_rmsnorm_rows(x, gain, eps=1e-5, split=False, device=0):
