@@ -201,7 +201,7 @@ int lm_head(llmc_engine* e, const float* xin, int64_t x_stride, int B, const int
   a.part_val = e->part_val; a.part_idx = e->part_idx; a.counter = e->lm_counter;
   a.next_token_out = e->d_next_token; a.seq_len_out = e->d_seq_len; a.seq_inc = seq_inc;
   a.out_tokens = out_tokens; a.out_stride = MAX_STEPS_PER_CALL; a.step_counter = step_counter;
-  E_TRY(launch_gemv(EPI_LMHEAD, PRO_NORM, batch_tile(B), a, pdl, e->stream));
+  E_TRY(launch_gemv_any(EPI_LMHEAD, PRO_NORM, a, pdl, e->stream));
   e->stats.kernel_launches++;
   return LLMC_OK;
 }
@@ -209,7 +209,7 @@ int lm_head(llmc_engine* e, const float* xin, int64_t x_stride, int B, const int
 // enqueue one decode step for the B sequences listed in d_slots
 int enqueue_decode_step(llmc_engine* e, int B, bool want_logits, int nsplit) {
   const ModelDims& d = e->d;
-  const int H = d.hidden, QD = d.qd(), I = d.inter, bt = batch_tile(B);
+  const int H = d.hidden, QD = d.qd(), I = d.inter;
   const bool pdl = e->use_pdl;
   for (int l = 0; l < d.layers; ++l) {
     const LayerW& w = e->L[l];
@@ -222,7 +222,7 @@ int enqueue_decode_step(llmc_engine* e, int B, bool want_logits, int nsplit) {
       a.emb = e->emb; a.x_out = e->x;
       a.y = e->q; a.y_stride = QD;
       a.kpool = kp; a.vpool = vp;
-      E_TRY(launch_gemv(EPI_QKV_ROPE, l == 0 ? PRO_EMBED_NORM : PRO_NORM, bt, a, pdl, e->stream));
+      E_TRY(launch_gemv_any(EPI_QKV_ROPE, l == 0 ? PRO_EMBED_NORM : PRO_NORM, a, pdl, e->stream));
     }
     {
       AttnDecodeArgs a;
@@ -239,21 +239,21 @@ int enqueue_decode_step(llmc_engine* e, int B, bool want_logits, int nsplit) {
       a.W = w.wo; a.N = H; a.K = QD;
       a.x = e->attn; a.x_stride = QD;
       a.y = e->x; a.y_stride = H;
-      E_TRY(launch_gemv(EPI_RESID, PRO_PLAIN, bt, a, pdl, e->stream));
+      E_TRY(launch_gemv_any(EPI_RESID, PRO_PLAIN, a, pdl, e->stream));
     }
     {  // act = silu(Wg h) * (Wu h), h = RMSNorm(x)
       GemvArgs a = base_args(e, B);
       a.W = w.wgu; a.N = 2 * I; a.K = H;
       a.x = e->x; a.x_stride = H; a.gain = w.g2;
       a.y = e->act; a.y_stride = I;
-      E_TRY(launch_gemv(EPI_SWIGLU, PRO_NORM, bt, a, pdl, e->stream));
+      E_TRY(launch_gemv_any(EPI_SWIGLU, PRO_NORM, a, pdl, e->stream));
     }
     {  // x += Wd act
       GemvArgs a = base_args(e, B);
       a.W = w.wd; a.N = H; a.K = I;
       a.x = e->act; a.x_stride = I;
       a.y = e->x; a.y_stride = H;
-      E_TRY(launch_gemv(EPI_RESID, PRO_PLAIN, bt, a, pdl, e->stream));
+      E_TRY(launch_gemv_any(EPI_RESID, PRO_PLAIN, a, pdl, e->stream));
     }
   }
   e->stats.kernel_launches += (uint64_t)d.layers * 5;
@@ -386,7 +386,7 @@ static int create_impl(llmc_engine* e, const llmc_config& c) {
   if (int rc = dalloc(e, &e->logits, (size_t)MB * V)) return rc;
   if (int rc = dalloc(e, &e->d_slots, MB)) return rc;
   if (int rc = dalloc(e, &e->d_pslot, 1)) return rc;
-  const int lmb = gemv_lmhead_blocks(V);
+  const int lmb = std::max(gemv_lmhead_blocks(V), gemv_mma_lmhead_blocks(V));
   if (int rc = dalloc(e, &e->part_val, (size_t)MB * lmb)) return rc;
   if (int rc = dalloc(e, &e->part_idx, (size_t)MB * lmb)) return rc;
   if (int rc = dalloc(e, &e->lm_counter, 1)) return rc;

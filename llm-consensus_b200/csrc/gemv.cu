@@ -408,12 +408,8 @@ cudaError_t launch_one(const GemvArgs& a, bool pdl, cudaStream_t s) {
 
 template <int EPI, int PRO>
 cudaError_t launch_bt(int bt, const GemvArgs& a, bool pdl, cudaStream_t s) {
-  switch (bt) {
-    case 1: return launch_one<EPI, PRO, 1>(a, pdl, s);
-    case 2: return launch_one<EPI, PRO, 2>(a, pdl, s);
-    case 4: return launch_one<EPI, PRO, 4>(a, pdl, s);
-    case 8: return launch_one<EPI, PRO, 8>(a, pdl, s);
-  }
+  // batches of 2..8 rows run on the tensor cores (gemv_mma.cu); this CUDA-core stream serves one row
+  if (bt == 1) return launch_one<EPI, PRO, 1>(a, pdl, s);
   return cudaErrorInvalidValue;
 }
 

@@ -60,6 +60,14 @@ cudaError_t launch_gemv(int epi, int pro, int bt, const GemvArgs& a, bool pdl, c
 // upper bound of blocks launch_gemv uses for an LM head of N rows (sizes part_val/part_idx)
 int gemv_lmhead_blocks(int N);
 
+// gemv_mma.cu: the same fused operation for 2..8 batch rows on the tensor cores (mma.sync tf32, batch = N)
+cudaError_t launch_gemv_mma(int epi, int pro, const GemvArgs& a, bool pdl, cudaStream_t s);
+int gemv_mma_lmhead_blocks(int N);
+// dispatcher used by the engine and the kernel hooks: 1 row -> CUDA-core stream, 2..8 rows -> tensor cores
+inline cudaError_t launch_gemv_any(int epi, int pro, const GemvArgs& a, bool pdl, cudaStream_t s) {
+  return a.B == 1 ? launch_gemv(epi, pro, 1, a, pdl, s) : launch_gemv_mma(epi, pro, a, pdl, s);
+}
+
 // ------------------------------------------------------------------ attn_decode.cu
 struct AttnDecodeArgs {
   const float* q;          // [B][q_heads*head_dim] fp32 (RoPE applied)

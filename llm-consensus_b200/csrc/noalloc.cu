@@ -109,8 +109,7 @@ int llmc_lmhead_argmax_noalloc(int device, int V, int K, int B, const uint16_t* 
   a.part_idx = reinterpret_cast<int*>(base + NA_PART_OFF + NA_PART_ELEMS * sizeof(float));
   a.out_tokens = d_tokens;  // step counter is 0, stride 1: token of batch row b lands in d_tokens[b]
   a.out_stride = 1;
-  const int bt = B <= 1 ? 1 : (B <= 2 ? 2 : (B <= 4 ? 4 : 8));
-  ce = launch_gemv(EPI_LMHEAD, PRO_NORM, bt, a, false, s);
+  ce = launch_gemv_any(EPI_LMHEAD, PRO_NORM, a, false, s);
   if (ce != cudaSuccess) return nfail(LLMC_ERR_CUDA, std::string("launch: ") + cudaGetErrorString(ce));
   return LLMC_OK;
 }

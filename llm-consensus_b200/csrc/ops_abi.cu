@@ -84,7 +84,7 @@ int llmc_op_gemv(int device, int N, int K, int B, const uint16_t* W, const float
   a.W = dW; a.N = N; a.K = K; a.B = B;
   a.x = dx; a.x_stride = K; a.gain = dg; a.eps = eps;
   a.y = dy; a.y_stride = N;
-  O_TRY(launch_gemv(resid ? EPI_RESID : EPI_STORE, norm ? PRO_NORM : PRO_PLAIN, batch_tile(B), a, false, 0));
+  O_TRY(launch_gemv_any(resid ? EPI_RESID : EPI_STORE, norm ? PRO_NORM : PRO_PLAIN, a, false, 0));
   O_TRY(cudaDeviceSynchronize());
   O_TRY(cudaMemcpy(y, dy, (size_t)B * N * sizeof(float), cudaMemcpyDeviceToHost));
   return LLMC_OK;
@@ -111,7 +111,7 @@ int llmc_op_gemv_swiglu(int device, int I, int K, int B, const uint16_t* Wg, con
   a.W = dW; a.N = 2 * I; a.K = K; a.B = B;
   a.x = dx; a.x_stride = K; a.gain = dg; a.eps = eps;
   a.y = dy; a.y_stride = I;
-  O_TRY(launch_gemv(EPI_SWIGLU, PRO_NORM, batch_tile(B), a, false, 0));
+  O_TRY(launch_gemv_any(EPI_SWIGLU, PRO_NORM, a, false, 0));
   O_TRY(cudaDeviceSynchronize());
   O_TRY(cudaMemcpy(act, dy, (size_t)B * I * sizeof(float), cudaMemcpyDeviceToHost));
   return LLMC_OK;
@@ -126,7 +126,7 @@ int llmc_op_lmhead(int device, int V, int K, int B, const uint16_t* W, const flo
   float *dx, *dl, *pv;
   int *pi, *slots, *next, *seq, *outtok, *step;
   unsigned* ctr;
-  const int nb = gemv_lmhead_blocks(V);
+  const int nb = gemv_lmhead_blocks(V) > gemv_mma_lmhead_blocks(V) ? gemv_lmhead_blocks(V) : gemv_mma_lmhead_blocks(V);
   O_TRY(pool.get(&dW, (size_t)V * K, W));
   O_TRY(pool.get(&dx, (size_t)B * K, x));
   O_TRY(pool.get(&dg, (size_t)K, gain));
@@ -151,7 +151,7 @@ int llmc_op_lmhead(int device, int V, int K, int B, const uint16_t* W, const flo
   a.next_token_out = next; a.seq_len_out = seq; a.seq_inc = 1;
   a.out_tokens = outtok; a.out_stride = 4; a.step_counter = step;
   // two launches: the second checks that counter/step state is left re-launchable
-  for (int rep = 0; rep < 2; ++rep) O_TRY(launch_gemv(EPI_LMHEAD, PRO_NORM, batch_tile(B), a, false, 0));
+  for (int rep = 0; rep < 2; ++rep) O_TRY(launch_gemv_any(EPI_LMHEAD, PRO_NORM, a, false, 0));
   O_TRY(cudaDeviceSynchronize());
   std::vector<int> ho((size_t)B * 4), hn(B), hq(B);
   int hstep = 0;
