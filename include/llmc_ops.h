@@ -61,10 +61,12 @@ int llmc_op_rmsnorm_rows(int device, int T, int H, const float* x, const uint16_
 /* RoPE + KV append + causal attention of T new rows at positions p0..p0+T-1:
  *   qkv [T][(nq+2nkv)*d] fp32 (pre-RoPE) for the new rows; k_past, v_past [p0][nkv*d] (already
  *   rotated) for the cached prefix, bf16 bits or fp32 per kv_fp32; out (+ out_lo, may be NULL)
- *   bf16 [T][nq*d]; q_out fp32 [T][nq*d]; k_new, v_new [T][nkv*d] read back from the pages. */
+ *   bf16 [T][nq*d]; q_out fp32 [T][nq*d]; k_new, v_new [T][nkv*d] read back from the pages.
+ *   impl 0: the engine's choice (tensor-core kernel for head_dim 64/128, GQA group 1/2/4, page_size % 64 == 0,
+ *   else the CUDA-core kernel); impl 1: always the CUDA-core kernel. */
 int llmc_op_prefill_attention(int device, int T, int p0, int q_heads, int kv_heads, int head_dim, int page_size,
                               float rope_theta, int kv_fp32, const float* qkv, const void* k_past, const void* v_past,
-                              uint16_t* out, uint16_t* out_lo, float* q_out, void* k_new, void* v_new);
+                              uint16_t* out, uint16_t* out_lo, float* q_out, void* k_new, void* v_new, int impl);
 
 /* Read a LOGICAL weight tensor of an engine back (un-packing the HBM layout); kinds as in the
  * oracle: layer -1: 0 embedding, 1 lm head, 2 final gain; layer >= 0: 0 g1, 1 wq, 2 wk, 3 wv,

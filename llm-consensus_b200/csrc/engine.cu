@@ -434,6 +434,8 @@ static int create_impl(llmc_engine* e, const llmc_config& c) {
     if (int rc = dalloc(e, &e->pattn_lo, (size_t)TC * QD)) return rc;
     if (int rc = dalloc(e, &e->pact_lo, (size_t)TC * I)) return rc;
   }
+  if (e->prefill_impl == 0 && prefill_attn_mma_supported(d.head_dim, d.q_heads / d.kv_heads))
+    if (int rc = dalloc(e, &e->pattn_ws, prefill_attn_mma_workspace_bytes(e->max_ctx, d.kv_heads, d.head_dim) / 2)) return rc;
   E_TRY(cudaStreamSynchronize(e->stream));
   E_TRY(cudaGetLastError());
   e->stats.graph_enabled = e->use_graph;
@@ -564,7 +566,8 @@ int llmc_prefill(llmc_engine* e, int32_t slot, const int32_t* tokens, int32_t n,
       E_TRY(launch_rope_append(e->pqkv, T, p0, slot, e->rope_cos, e->rope_sin, e->d_block_table, e->pages_per_seq,
                                kp, vp, e->kv_fp32, e->page_size, d.q_heads, d.kv_heads, d.head_dim, e->pq, s));
       E_TRY(launch_prefill_attention(e->pq, T, p0, slot, e->d_block_table, e->pages_per_seq, kp, vp, e->kv_fp32,
-                                     e->page_size, d.q_heads, d.kv_heads, d.head_dim, e->pattn, e->pattn_lo, s));
+                                     e->page_size, d.q_heads, d.kv_heads, d.head_dim, e->pattn, e->pattn_lo, e->pattn_ws,
+                                     e->prefill_impl, s));
       if (int rc = gemm(e, e->pattn, e->pattn_lo, w.wo, e->px, nullptr, T, H, QD, GEMM_RESID_F32)) return rc;
       E_TRY(launch_rmsnorm_rows(e->px, w.g2, d.rms_eps, T, H, e->pxn, e->pxn_lo, s));
       if (int rc = gemm(e, e->pxn, e->pxn_lo, w.wgu, e->pact, e->pact_lo, T, 2 * I, H, GEMM_SWIGLU_BF16)) return rc;

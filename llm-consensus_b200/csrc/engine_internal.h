@@ -57,6 +57,7 @@ struct llmc_engine {
   float *px = nullptr, *pqkv = nullptr, *pq = nullptr;
   uint16_t *pxn = nullptr, *pattn = nullptr, *pact = nullptr;
   uint16_t *pxn_lo = nullptr, *pattn_lo = nullptr, *pact_lo = nullptr;  // split-bf16 low halves (or NULL)
+  uint16_t* pattn_ws = nullptr;  // split K/V workspace of the tensor-core prefill attention (one layer, max_ctx positions)
   // one-kernel batch-1 decode
   bool use_mega = true;
   llmc::MegaLayer* d_mega_layers = nullptr;

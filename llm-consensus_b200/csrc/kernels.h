@@ -133,11 +133,21 @@ cudaError_t launch_rope_append(const float* qkv, int T, int p0, int slot, const 
                                const float* rope_sin, const int* block_table, int bt_stride, void* kpool,
                                void* vpool, int kv_fp32, int page_size, int q_heads, int kv_heads, int head_dim,
                                float* q_out, cudaStream_t s);
-// causal attention of T new rows (positions p0..p0+T-1) over the paged cache; out bf16 [T][qd] (hi, lo)
+// causal attention of T new rows (positions p0..p0+T-1) over the paged cache; out bf16 [T][qd] (hi, lo).
+// impl 0: tensor-core kernel (prefill_attn_mma.cu) whenever the shape allows it and a workspace is given, else the
+// CUDA-core kernel; impl 1: always the CUDA-core kernel (comparator).
 cudaError_t launch_prefill_attention(const float* q, int T, int p0, int slot, const int* block_table,
                                      int bt_stride, const void* kpool, const void* vpool, int kv_fp32, int page_size,
                                      int q_heads, int kv_heads, int head_dim, uint16_t* out_hi, uint16_t* out_lo,
-                                     cudaStream_t s);
+                                     uint16_t* mma_workspace, int impl, cudaStream_t s);
+// ------------------------------------------------------------------ prefill_attn_mma.cu
+bool prefill_attn_mma_supported(int head_dim, int G);
+// split-KV workspace for sequences of up to max_positions cached positions (one layer at a time)
+size_t prefill_attn_mma_workspace_bytes(int max_positions, int kv_heads, int head_dim);
+cudaError_t launch_prefill_attention_mma(const float* q, int T, int p0, int slot, const int* block_table,
+                                         int bt_stride, const void* kpool, const void* vpool, int kv_fp32,
+                                         int page_size, int q_heads, int kv_heads, int head_dim, uint16_t* out_hi,
+                                         uint16_t* out_lo, uint16_t* workspace, cudaStream_t s);
 
 // ------------------------------------------------------------------ gemm_tcgen05.cu / gemm_simple.cu (prefill)
 // C[T][N] = (A_hi [+ A_lo])[T][K] (bf16) * W[N][K]^T (bf16), fp32 accumulation.  A_lo may be NULL.

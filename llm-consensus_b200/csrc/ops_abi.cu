@@ -324,7 +324,7 @@ int llmc_op_rmsnorm_rows(int device, int T, int H, const float* x, const uint16_
 
 int llmc_op_prefill_attention(int device, int T, int p0, int q_heads, int kv_heads, int head_dim, int page_size,
                               float rope_theta, int kv_fp32, const float* qkv, const void* k_past, const void* v_past,
-                              uint16_t* out, uint16_t* out_lo, float* q_out, void* k_new, void* v_new) {
+                              uint16_t* out, uint16_t* out_lo, float* q_out, void* k_new, void* v_new, int impl) {
   if (!qkv || !out || T < 1 || p0 < 0 || (p0 > 0 && (!k_past || !v_past)) || page_size < 32 || page_size % 32)
     return ofail(LLMC_ERR_INVALID, "llmc_op_prefill_attention: bad argument");
   O_TRY(cudaSetDevice(device));
@@ -367,7 +367,15 @@ int llmc_op_prefill_attention(int device, int T, int p0, int q_heads, int kv_hea
   O_TRY(pool.get(&ds, hs.size(), hs.data()));
   O_TRY(pool.get(&dbt, bt.size(), bt.data()));
   O_TRY(launch_rope_append(dqkv, T, p0, 0, dc, ds, dbt, pps, dk, dv, kv_fp32, page_size, q_heads, kv_heads, D, dq, 0));
-  O_TRY(launch_prefill_attention(dq, T, p0, 0, dbt, pps, dk, dv, kv_fp32, page_size, q_heads, kv_heads, D, dout, dlo, 0));
+  uint16_t* dws = nullptr;
+  if (impl == 0 && q_heads % kv_heads == 0 && prefill_attn_mma_supported(D, q_heads / kv_heads))
+  {
+    const size_t wsb = prefill_attn_mma_workspace_bytes(total, kv_heads, D);
+    O_TRY(pool.get(&dws, wsb / 2));
+    O_TRY(cudaMemset(dws, 0xFF, wsb));   // NaN poison: the kernel must never consume a byte it did not write
+  }
+  O_TRY(launch_prefill_attention(dq, T, p0, 0, dbt, pps, dk, dv, kv_fp32, page_size, q_heads, kv_heads, D, dout, dlo, dws,
+                                 impl, 0));
   O_TRY(cudaDeviceSynchronize());
   O_TRY(cudaMemcpy(out, dout, (size_t)T * QD * 2, cudaMemcpyDeviceToHost));
   if (out_lo) O_TRY(cudaMemcpy(out_lo, dlo, (size_t)T * QD * 2, cudaMemcpyDeviceToHost));

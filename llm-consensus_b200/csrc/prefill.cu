@@ -256,9 +256,12 @@ cudaError_t launch_rope_append(const float* qkv, int T, int p0, int slot, const 
 cudaError_t launch_prefill_attention(const float* q, int T, int p0, int slot, const int* block_table,
                                      int bt_stride, const void* kpool, const void* vpool, int kv_fp32, int page_size,
                                      int q_heads, int kv_heads, int head_dim, uint16_t* out_hi, uint16_t* out_lo,
-                                     cudaStream_t s) {
+                                     uint16_t* mma_workspace, int impl, cudaStream_t s) {
   if (q_heads % kv_heads != 0 || page_size % ATT_TP != 0) return cudaErrorInvalidValue;
   const int G = q_heads / kv_heads;
+  if (impl == 0 && mma_workspace && prefill_attn_mma_supported(head_dim, G))
+    return launch_prefill_attention_mma(q, T, p0, slot, block_table, bt_stride, kpool, vpool, kv_fp32, page_size,
+                                        q_heads, kv_heads, head_dim, out_hi, out_lo, mma_workspace, s);
   if (kv_fp32)
     return launch_pa_d<float>(head_dim, G, q, T, p0, slot, block_table, bt_stride, kpool, vpool, page_size, q_heads,
                               kv_heads, out_hi, out_lo, s);

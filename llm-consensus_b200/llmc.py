@@ -84,7 +84,7 @@ def lib():
         l.llmc_op_gemm.argtypes = [C.c_int] * 6 + [vp] * 5
         l.llmc_op_gemm_bench.argtypes = [C.c_int] * 8 + [vp]
         l.llmc_op_rmsnorm_rows.argtypes = [C.c_int] * 3 + [vp, vp, C.c_float, vp, vp]
-        l.llmc_op_prefill_attention.argtypes = [C.c_int] * 7 + [C.c_float, C.c_int] + [vp] * 8
+        l.llmc_op_prefill_attention.argtypes = [C.c_int] * 7 + [C.c_float, C.c_int] + [vp] * 8 + [C.c_int]
         l.llmc_debug_tensor.argtypes = [vp, C.c_int, C.c_int, vp, C.c_int64]
         l.llmc_debug_tensor.restype = C.c_int64
         l.llmc_debug_kv.argtypes = [vp, C.c_int, C.c_int, C.c_int, vp, vp]
@@ -306,7 +306,7 @@ def op_rmsnorm_rows(x, gain, eps=1e-5, split=False, device=0):
 
 
 def op_prefill_attention(qkv, k_past, v_past, q_heads, kv_heads, head_dim, page_size=64, rope_theta=500000.0,
-                         kv_fp32=True, split=True, device=0):
+                         kv_fp32=True, split=True, device=0, impl=0):
     """Returns (out_hi, out_lo | None, q fp32, k_new, v_new); k/v arrays are float32 or uint16 (bf16 bits)."""
     dt = np.float32 if kv_fp32 else np.uint16
     qkv = _c(qkv, np.float32)
@@ -321,5 +321,5 @@ def op_prefill_attention(qkv, k_past, v_past, q_heads, kv_heads, head_dim, page_
     kn = np.zeros((T, KD), dt); vn = np.zeros((T, KD), dt)
     _ops_check(lib().llmc_op_prefill_attention(device, T, p0, q_heads, kv_heads, head_dim, page_size, rope_theta,
                                                int(kv_fp32), qkv.ctypes.data, _ptr(kp), _ptr(vp), out.ctypes.data,
-                                               _ptr(lo), qo.ctypes.data, kn.ctypes.data, vn.ctypes.data))
+                                               _ptr(lo), qo.ctypes.data, kn.ctypes.data, vn.ctypes.data, impl))
     return out, lo, qo, kn, vn

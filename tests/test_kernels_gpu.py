@@ -122,10 +122,12 @@ def test_rmsnorm_rows(gpu, T, H):
     assert np.abs(pair - want).max() <= 2 ** -15 * np.abs(want).max() + 1e-6
 
 
-@pytest.mark.parametrize("nq,nkv,d", [(8, 2, 32), (32, 8, 64), (4, 2, 128), (4, 4, 64)])
-@pytest.mark.parametrize("T,p0,page", [(1, 0, 64), (20, 0, 32), (70, 0, 64), (9, 100, 64), (130, 61, 32)])
+@pytest.mark.parametrize("impl", [0, 1])   # 0: tensor-core kernel where the shape allows it; 1: CUDA-core kernel
+@pytest.mark.parametrize("nq,nkv,d", [(8, 2, 32), (32, 8, 64), (4, 2, 128), (4, 4, 64), (16, 4, 128), (8, 1, 64)])
+@pytest.mark.parametrize("T,p0,page", [(1, 0, 64), (20, 0, 32), (70, 0, 64), (9, 100, 64), (130, 61, 32),
+                                       (130, 61, 64), (33, 200, 128)])
 @pytest.mark.parametrize("fp32", [True, False])
-def test_rope_append_and_prefill_attention(gpu, nq, nkv, d, T, p0, page, fp32):
+def test_rope_append_and_prefill_attention(gpu, nq, nkv, d, T, p0, page, fp32, impl):
     rng = np.random.default_rng(nq + d + T + p0)
     QD, KD = nq * d, nkv * d
     qkv = rng.standard_normal((T, QD + 2 * KD)).astype(np.float32)
@@ -137,7 +139,7 @@ def test_rope_append_and_prefill_attention(gpu, nq, nkv, d, T, p0, page, fp32):
         kp = rnd_bf16(rng, (p0, KD)) if p0 else None
         vp = rnd_bf16(rng, (p0, KD)) if p0 else None
         widen = lnp.bf16_to_f32
-    out, lo, qo, kn, vn = gpu.op_prefill_attention(qkv, kp, vp, nq, nkv, d, page, kv_fp32=fp32, split=True)
+    out, lo, qo, kn, vn = gpu.op_prefill_attention(qkv, kp, vp, nq, nkv, d, page, kv_fp32=fp32, split=True, impl=impl)
     cos, sin = lnp.rope_tables(p0 + T, d)
     pos = np.arange(p0, p0 + T)
     q_want = lnp.rope(qkv[:, :QD].reshape(T, nq, d), pos, cos, sin)
@@ -160,6 +162,22 @@ def test_rope_append_and_prefill_attention(gpu, nq, nkv, d, T, p0, page, fp32):
         want = lnp.attention(qf[t], k_all[:p0 + t + 1], v_all[:p0 + t + 1])
         assert np.abs(hi[t] - want).max() <= 2 ** -8 * np.abs(want).max() + 1e-4, t
         assert np.abs(pair[t] - want).max() <= 2e-4 * np.abs(want).max() + 1e-5, t
+
+
+def test_prefill_attention_tensor_core_matches_cuda_core(gpu):
+    """Full-size head geometry (32 q / 8 kv heads x 64, and 128), a prompt longer than several tiles, with a
+    cached prefix: the tensor-core kernel (3 x tf32 split products) must agree with the CUDA-core fp32 kernel to
+    the rounding of the bf16 hi+lo output pair."""
+    for nq, nkv, d in [(32, 8, 64), (32, 8, 128)]:
+        rng = np.random.default_rng(d)
+        T, p0 = 300, 77
+        QD, KD = nq * d, nkv * d
+        qkv = rng.standard_normal((T, QD + 2 * KD)).astype(np.float32)
+        kp = rng.standard_normal((p0, KD)).astype(np.float32)
+        vp = rng.standard_normal((p0, KD)).astype(np.float32)
+        res = [gpu.op_prefill_attention(qkv, kp, vp, nq, nkv, d, 64, kv_fp32=True, split=True, impl=i) for i in (0, 1)]
+        pair = [lnp.bf16_to_f32(r[0]) + lnp.bf16_to_f32(r[1]) for r in res]
+        assert np.abs(pair[0] - pair[1]).max() <= 2e-5 * np.abs(pair[1]).max()
 
 
 def run_gemm_check(T, N, K, epi, impl, split=0, timeout=120):
