@@ -337,6 +337,9 @@ static int create_impl(llmc_engine* e, const llmc_config& c) {
   e->kv_elem = e->kv_fp32 ? 4 : 2;
   e->split_prefill = !(c.flags & LLMC_FLAG_PREFILL_BF16);
   e->use_mega = !(c.flags & LLMC_FLAG_NO_MEGAKERNEL);
+  e->use_ring = e->use_mega && !(c.flags & LLMC_FLAG_NO_RING) &&
+                decode_ring_supported(e->d.hidden, e->d.qd(), e->d.kd(), e->d.inter, e->d.vocab, e->d.q_heads, e->d.kv_heads,
+                                      e->d.head_dim);
   e->stats.sm_count = e->prop.multiProcessorCount; e->stats.cc_major = e->prop.major; e->stats.cc_minor = e->prop.minor;
   E_TRY(cudaStreamCreateWithFlags(&e->stream, cudaStreamNonBlocking));
   E_TRY(cudaEventCreate(&e->ev0));
@@ -417,7 +420,7 @@ static int create_impl(llmc_engine* e, const llmc_config& c) {
     if (int rc = dalloc(e, &e->mega_barrier, 1)) return rc;
     if (int rc = dalloc(e, &e->mega_counters, (size_t)d.kv_heads)) return rc;
     if (getenv("LLMC_MEGA_TRACE"))
-      if (int rc = dalloc(e, &e->mega_trace, (size_t)2 * (5 * d.layers + 1) * 64)) return rc;
+      if (int rc = dalloc(e, &e->mega_trace, (size_t)2 * (5 * d.layers + 1) * 64 + 16)) return rc;
     E_TRY(cudaMemsetAsync(e->mega_counters, 0, (size_t)d.kv_heads * sizeof(unsigned), e->stream));
   }
   // ---- prefill workspace
@@ -639,7 +642,8 @@ static int decode_group(llmc_engine* e, const int32_t* slots, int32_t nslots, in
     }
     m.trace = (e->mega_trace && nsteps <= 64) ? e->mega_trace : nullptr;
     E_TRY(cudaMemsetAsync(e->mega_barrier, 0, sizeof(unsigned), s));
-    E_TRY(launch_decode_mega(m, e->prop.multiProcessorCount, s));
+    if (e->use_ring) E_TRY(launch_decode_ring(m, e->prop.multiProcessorCount, s));
+    else E_TRY(launch_decode_mega(m, e->prop.multiProcessorCount, s));
     e->stats.kernel_launches += 1;
   }
   for (int st = 0; st < nsteps && !mega; ++st) {
@@ -662,7 +666,7 @@ static int decode_group(llmc_engine* e, const int32_t* slots, int32_t nslots, in
   if (mega && e->mega_trace && nsteps <= 64) {
     // debug trace: average per-phase time (barrier open -> next barrier open) and barrier wait of block 0
     const int nb = (5 * d.layers + 1) * nsteps;
-    std::vector<unsigned long long> t((size_t)2 * nb);
+    std::vector<unsigned long long> t((size_t)2 * nb + 16);
     E_TRY(cudaMemcpy(t.data(), e->mega_trace, t.size() * sizeof(unsigned long long), cudaMemcpyDeviceToHost));
     const char* names[6] = {"qkv", "attn", "o", "gateup", "down", "lmhead"};
     double phase[6] = {0, 0, 0, 0, 0, 0}, wait[6] = {0, 0, 0, 0, 0, 0};
@@ -677,6 +681,12 @@ static int decode_group(llmc_engine* e, const int32_t* slots, int32_t nslots, in
     for (int k = 0; k < 6; ++k)
       if (cnt[k]) fprintf(stderr, "[mega trace] %-7s phase %.2f us (block 0 waited %.2f us at its barrier) x%d\n", names[k],
                           phase[k] / cnt[k] / 1e3, wait[k] / cnt[k] / 1e3, cnt[k]);
+    if (e->use_ring) {
+      const unsigned long long* st = t.data() + (size_t)2 * nb;
+      fprintf(stderr, "[ring stats] block 0 warp 0, cycles: total %llu = wait-full %llu + x-load %llu + slots %llu (%llu slots seen) "
+                      "+ grid barriers %llu; producer: total %llu, wait-empty %llu, %llu slots\n",
+              st[4], st[0], st[1], st[2], st[5], st[3], st[9], st[8], st[10]);
+    }
   }
   if (out_tokens) memcpy(out_tokens, host.data(), host.size() * sizeof(int));
   for (int i = 0; i < nslots; ++i) e->h_seq_len[slots[i]] += nsteps;

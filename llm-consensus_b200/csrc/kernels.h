@@ -121,6 +121,10 @@ struct MegaArgs {
   int smem_x;                  // filled by the launcher
 };
 cudaError_t launch_decode_mega(const MegaArgs& a, int sm_count, cudaStream_t s);
+// ------------------------------------------------------------------ decode_ring.cu
+// same contract as launch_decode_mega; weights travel through a per-SM shared-memory ring filled by TMA bulk copies
+bool decode_ring_supported(int H, int QD, int KD, int I, int V, int q_heads, int kv_heads, int head_dim);
+cudaError_t launch_decode_ring(const MegaArgs& a, int sm_count, cudaStream_t s);
 
 // ------------------------------------------------------------------ prefill.cu
 cudaError_t launch_embed_rows(const uint16_t* emb, const int* tokens, int T, int H, float* x, cudaStream_t s);

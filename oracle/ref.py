@@ -30,6 +30,14 @@ SHAPES = {
                         vocab=1000, tied=0),
     "small-d128": dict(hidden=512, layers=3, q_heads=4, kv_heads=2, head_dim=128, inter=1024,
                        vocab=2048, tied=0),
+    # hidden = 2048 shapes with few layers / a small vocabulary: the widths the shared-memory-ring decode
+    # kernel handles (rows of 2048 / 4096 / 8192 elements), cheap enough for the CPU oracle
+    "wide-1b": dict(hidden=2048, layers=2, q_heads=32, kv_heads=8, head_dim=64, inter=8192,
+                    vocab=4096, tied=1),
+    "wide-d128": dict(hidden=2048, layers=2, q_heads=32, kv_heads=8, head_dim=128, inter=4096,
+                      vocab=2048, tied=0),
+    "wide-mha": dict(hidden=2048, layers=1, q_heads=16, kv_heads=16, head_dim=128, inter=2048,
+                     vocab=1024, tied=0),
 }
 
 K_EMB, K_LMHEAD, K_FINAL_NORM = 0, 1, 2

@@ -111,6 +111,50 @@ def test_teacher_forced_decode_logits(gpu, name, flags):
     e.close()
 
 
+WIDE = ["wide-1b", "wide-d128", "wide-mha"]
+
+
+@pytest.mark.parametrize("flags", [0, 32, 4, 36])   # 0: shared-memory-ring kernel; 32: register-streaming kernel; 4: bf16 KV
+@pytest.mark.parametrize("name", WIDE)
+def test_ring_decode_teacher_forced_logits(gpu, name, flags):
+    """The persistent decode kernels at hidden = 2048 (the ring kernel's shapes: rows of 2048 / 4096 / 8192
+    elements, head sizes 64 / 128, GQA groups 4 / 1): every step's logits against the oracle, teacher-forced."""
+    o, e = make_pair(gpu, name, seed=5, flags=flags, max_ctx=256, max_slots=1)
+    V = DIMS[name]["vocab"]
+    prompt = np.random.default_rng(11).integers(0, V, 45)
+    n_new = 24
+    otoks, olog = o.generate(prompt, n_new, want_logits=True)
+    slot = e.seq_alloc()
+    nxt, lg = e.prefill(slot, prompt, want_logits=True)
+    worst = np.abs(lg - olog[0]).max()
+    for s in range(1, n_new):
+        e.set_next_token(slot, otoks[s - 1])
+        out, lg = e.decode([slot], 1, want_logits=True)
+        worst = max(worst, np.abs(lg[0] - olog[s]).max())
+        assert out[0, 0] == int(np.argmax(lg[0]))
+    tol = TOL if not flags & 4 else 6e-2    # bf16 KV is the reduced-precision mode (see test_reduced_precision_modes)
+    assert worst <= tol, "decode logits max-abs %.3e" % worst
+    print("%s flags %d: worst logit err %.2e" % (name, flags, worst))
+    e.close()
+
+
+@pytest.mark.parametrize("name", WIDE)
+@pytest.mark.parametrize("chunk", [1, 5, 64])
+def test_ring_decode_free_running_matches_register_kernel(gpu, name, chunk):
+    """Free-running greedy decode, many steps per call: ring kernel vs oracle, and token-identical to the
+    register-streaming kernel (same arithmetic order per row is not guaranteed, so compare through the oracle's
+    tie rule)."""
+    o, e = make_pair(gpu, name, seed=14, max_ctx=256, max_slots=1)
+    V = DIMS[name]["vocab"]
+    prompt = np.random.default_rng(2).integers(0, V, 70)
+    n_new = 64
+    otoks, olog = o.generate(prompt, n_new, want_logits=True)
+    gtoks = e.generate(prompt, n_new, chunk=chunk)
+    where, margin = greedy_agreement(otoks, olog, gtoks)
+    assert where < 0, "greedy tokens diverge at step %d with oracle margin %.3e > tol" % (where, margin)
+    e.close()
+
+
 def greedy_agreement(otoks, olog, gtoks, tol=TOL):
     """Index of the first free-running disagreement that is NOT a numerical tie in the oracle, or -1."""
     for s, (a, b) in enumerate(zip(otoks, gtoks)):
