@@ -186,7 +186,7 @@ def run_ours(args, rank, world, local_rank):
     tokens_all = NEW_TOKENS * args.steps * world
     value = tokens_all / (dev_ms / 1e3)
     e2e = tokens_all / wall_s
-    # roofline of the decode step (one CUDA-graph launch = 81 kernels): algorithmic bytes / device time
+    # roofline of the decode step (one pass of the persistent kernel over all weights): algorithmic bytes / device time
     steps_dec = (NEW_TOKENS - 1) * args.steps
     avg_ctx = PROMPT_LEN + (NEW_TOKENS - 1) / 2.0
     bytes_per_step = st["weight_bytes"] + (avg_ctx + 1) * st["kv_bytes_per_token"]
@@ -194,7 +194,7 @@ def run_ours(args, rank, world, local_rank):
     peak, peak_src = peaks()
     achieved = bytes_per_step / step_s / 1e9
     traffic = None
-    tp = os.path.join(ROOT, "profiles", "r1_mega_traffic.json")
+    tp = os.path.join(ROOT, "profiles", "r1_ring_traffic.json")
     if os.path.exists(tp):
         traffic = json.load(open(tp))["dram_bytes_per_step"]
     line = {
@@ -206,7 +206,7 @@ def run_ours(args, rank, world, local_rank):
                                "no collective",
                    "shape": "llama-3.2-1b", "prompt": PROMPT_LEN, "new_tokens": NEW_TOKENS, "batch": 1,
                    "l2": "no flush needed: each decode step streams 2.47 GB of weights, 20x the 126 MB L2",
-                   "decode_path": "persistent cooperative kernel (batch 1)", "kv_cache": "fp32",
+                   "decode_path": "persistent cooperative kernel, weights through a TMA-fed shared-memory ring (batch 1)", "kv_cache": "fp32",
                    "prefill_operands": "bf16 hi+lo pairs"},
         "decode_only_tok_s_per_gpu": steps_dec / (dec_ms / 1e3),
         "prefill_ms": pre_ms / args.steps,
@@ -218,9 +218,10 @@ def run_ours(args, rank, world, local_rank):
         "gpu_launches": int(launches_all),
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                      "traffic": traffic, "peak_source": peak_src, "frac_of_8TBs_nominal": achieved / 8000.0,
-                     "kernel": "decode_mega_kernel: one persistent cooperative kernel runs every decode step of a "
+                     "kernel": "decode_ring_kernel: one persistent cooperative kernel runs every decode step of a "
                                "llmc_decode call (5 phases/layer x 16 + LM head per step); figures are per step",
-                     "traffic_source": "profiles/r1_mega_traffic.json (ncu --set full, dram__bytes_read.sum / steps)",
+                     "traffic_source": "profiles/r1_ring_traffic.json (ncu --set full, (dram__bytes_read.sum + "
+                                       "dram__bytes_write.sum) / steps)",
                      "algorithmic_bytes_per_launch": bytes_per_step, "avg_launch_us": step_s * 1e6},
         "clocks": clocks,
     }

@@ -317,21 +317,23 @@ __global__ void __launch_bounds__(RTHREADS, 1) decode_ring_kernel(const MegaArgs
       const long long tf1 = stats ? clock64() : 0;
       if (stats) t_full += tf1 - tf0;
       const uint32_t base = ring_s + r * SLOT_BYTES;
-      float acc0 = 0.f, acc1 = 0.f;
+      // two independent chains per row keep the FMA dependency depth at 32
+      float a0 = 0.f, a1 = 0.f, b0 = 0.f, b1 = 0.f;
 #pragma unroll
       for (int c = 0; c < SEG / 256; ++c) {
         const uint4 wa = lds128(base + offA + c * 512);
         const uint4 wb = lds128(base + offB + c * 512);
         const float* x = xr + c * 8;
-        acc0 = fmaf(bf16lo(wa.x), x[0], acc0); acc0 = fmaf(bf16hi(wa.x), x[1], acc0);
-        acc0 = fmaf(bf16lo(wa.y), x[2], acc0); acc0 = fmaf(bf16hi(wa.y), x[3], acc0);
-        acc0 = fmaf(bf16lo(wa.z), x[4], acc0); acc0 = fmaf(bf16hi(wa.z), x[5], acc0);
-        acc0 = fmaf(bf16lo(wa.w), x[6], acc0); acc0 = fmaf(bf16hi(wa.w), x[7], acc0);
-        acc1 = fmaf(bf16lo(wb.x), x[0], acc1); acc1 = fmaf(bf16hi(wb.x), x[1], acc1);
-        acc1 = fmaf(bf16lo(wb.y), x[2], acc1); acc1 = fmaf(bf16hi(wb.y), x[3], acc1);
-        acc1 = fmaf(bf16lo(wb.z), x[4], acc1); acc1 = fmaf(bf16hi(wb.z), x[5], acc1);
-        acc1 = fmaf(bf16lo(wb.w), x[6], acc1); acc1 = fmaf(bf16hi(wb.w), x[7], acc1);
+        a0 = fmaf(bf16lo(wa.x), x[0], a0); a1 = fmaf(bf16hi(wa.x), x[1], a1);
+        a0 = fmaf(bf16lo(wa.y), x[2], a0); a1 = fmaf(bf16hi(wa.y), x[3], a1);
+        a0 = fmaf(bf16lo(wa.z), x[4], a0); a1 = fmaf(bf16hi(wa.z), x[5], a1);
+        a0 = fmaf(bf16lo(wa.w), x[6], a0); a1 = fmaf(bf16hi(wa.w), x[7], a1);
+        b0 = fmaf(bf16lo(wb.x), x[0], b0); b1 = fmaf(bf16hi(wb.x), x[1], b1);
+        b0 = fmaf(bf16lo(wb.y), x[2], b0); b1 = fmaf(bf16hi(wb.y), x[3], b1);
+        b0 = fmaf(bf16lo(wb.z), x[4], b0); b1 = fmaf(bf16hi(wb.z), x[5], b1);
+        b0 = fmaf(bf16lo(wb.w), x[6], b0); b1 = fmaf(bf16hi(wb.w), x[7], b1);
       }
+      float acc0 = a0 + a1, acc1 = b0 + b1;
       __syncwarp();
       if (lane == 0) mbar_arrive(empty_bar(r));   // the slot's bytes are in registers: hand it back
       acc0 = warp_sum(acc0);
@@ -471,20 +473,28 @@ __global__ void __launch_bounds__(RTHREADS, 1) decode_ring_kernel(const MegaArgs
                 for (int i = 0; i < DPL; ++i) O[i] = fmaf(pp[lane * DPL + i], wt, O[i]);
               }
             }
-            float* rec = a.attn_scratch + (((size_t)kvh * RING_MAX_SPLIT + split) * G + h) * PS;
+            if (nsp == 1) {   // the block saw the whole context: done, no cross-block merge
+              const float inv = 1.0f / L;
 #pragma unroll
-            for (int i = 0; i < DPL; ++i) rec[lane * DPL + i] = O[i];
-            if (lane == 0) {
-              rec[D] = M;
-              rec[D + 1] = L;
+              for (int i = 0; i < DPL; ++i) a.attn[(size_t)(kvh * G + h) * D + lane * DPL + i] = O[i] * inv;
+            } else {
+              float* rec = a.attn_scratch + (((size_t)kvh * RING_MAX_SPLIT + split) * G + h) * PS;
+#pragma unroll
+              for (int i = 0; i < DPL; ++i) rec[lane * DPL + i] = O[i];
+              if (lane == 0) {
+                rec[D] = M;
+                rec[D + 1] = L;
+              }
             }
           }
           // the last block to finish this kv head merges its nsp split records
-          __threadfence();
-          cbar();
-          if (tid == 0) s_last = (atomicAdd(a.attn_counters + kvh, 1u) == (unsigned)(nsp - 1)) ? 1 : 0;
-          cbar();
-          if (s_last && warp < G) {
+          if (nsp > 1) {
+            __threadfence();
+            cbar();
+            if (tid == 0) s_last = (atomicAdd(a.attn_counters + kvh, 1u) == (unsigned)(nsp - 1)) ? 1 : 0;
+            cbar();
+          }
+          if (nsp > 1 && s_last && warp < G) {
             __threadfence();
             constexpr int DPL = D / 32;
             const int h = warp;
