@@ -206,8 +206,50 @@ int lm_head(llmc_engine* e, const float* xin, int64_t x_stride, int B, const int
   return LLMC_OK;
 }
 
+// One decode step of 9..128 sequences: the matrix products are skinny GEMMs on the tcgen05 kernel of the prefill
+// (batch = M tile, every weight streamed once), around them the per-sequence bookkeeping of decode_wide.cu.  Uses
+// the prefill workspace (prefill and decode never overlap: both hold the engine mutex).
+int enqueue_wide_step(llmc_engine* e, int B, int nsplit) {
+  const ModelDims& d = e->d;
+  const int H = d.hidden, QD = d.qd(), KD = d.kd(), I = d.inter, V = d.vocab;
+  cudaStream_t s = e->stream;
+  E_TRY(launch_embed_slots(e->emb, e->d_next_token, e->d_slots, B, H, e->px, s));
+  for (int l = 0; l < d.layers; ++l) {
+    const LayerW& w = e->L[l];
+    unsigned char* kp = e->kpool + (size_t)l * e->kv_layer_stride * e->kv_elem;
+    unsigned char* vp = e->vpool + (size_t)l * e->kv_layer_stride * e->kv_elem;
+    E_TRY(launch_rmsnorm_rows(e->px, w.g1, d.rms_eps, B, H, e->pxn, e->pxn_lo, s));
+    if (int rc = gemm(e, e->pxn, e->pxn_lo, w.wqkv, e->pqkv, nullptr, B, QD + 2 * KD, H, GEMM_STORE_F32)) return rc;
+    E_TRY(launch_rope_append_batch(e->pqkv, B, e->d_slots, e->d_seq_len, e->rope_cos, e->rope_sin, e->d_block_table,
+                                   e->pages_per_seq, kp, vp, e->kv_fp32, e->page_size, d.q_heads, d.kv_heads,
+                                   d.head_dim, e->q, s));
+    {
+      AttnDecodeArgs a;
+      memset(&a, 0, sizeof(a));
+      a.q = e->q; a.out = e->attn; a.kpool = kp; a.vpool = vp; a.kv_fp32 = e->kv_fp32;
+      a.slots = e->d_slots; a.seq_len = e->d_seq_len; a.ctx_extra = 1;
+      a.block_table = e->d_block_table; a.bt_stride = e->pages_per_seq;
+      a.page_size = e->page_size; a.q_heads = d.q_heads; a.kv_heads = d.kv_heads; a.head_dim = d.head_dim;
+      a.B = B; a.nsplit = nsplit; a.scratch = e->attn_scratch; a.counters = e->attn_counters;
+      E_TRY(launch_attn_decode(a, false, s));
+    }
+    E_TRY(launch_split_rows(e->attn, (size_t)B * QD, e->pattn, e->pattn_lo, s));
+    if (int rc = gemm(e, e->pattn, e->pattn_lo, w.wo, e->px, nullptr, B, H, QD, GEMM_RESID_F32)) return rc;
+    E_TRY(launch_rmsnorm_rows(e->px, w.g2, d.rms_eps, B, H, e->pxn, e->pxn_lo, s));
+    if (int rc = gemm(e, e->pxn, e->pxn_lo, w.wgu, e->pact, e->pact_lo, B, 2 * I, H, GEMM_SWIGLU_BF16)) return rc;
+    if (int rc = gemm(e, e->pact, e->pact_lo, w.wd, e->px, nullptr, B, H, I, GEMM_RESID_F32)) return rc;
+  }
+  E_TRY(launch_rmsnorm_rows(e->px, e->gf, d.rms_eps, B, H, e->pxn, e->pxn_lo, s));
+  if (int rc = gemm(e, e->pxn, e->pxn_lo, e->lmhead, e->logits, nullptr, B, V, H, GEMM_STORE_F32)) return rc;
+  E_TRY(launch_argmax_finalise(e->logits, B, V, e->d_slots, e->d_next_token, e->d_seq_len, e->d_out_tokens,
+                               MAX_STEPS_PER_CALL, e->d_step_counter, e->lm_counter, s));
+  e->stats.kernel_launches += (uint64_t)d.layers * 5 + 3;   // the GEMMs count themselves
+  return LLMC_OK;
+}
+
 // enqueue one decode step for the B sequences listed in d_slots
 int enqueue_decode_step(llmc_engine* e, int B, bool want_logits, int nsplit) {
+  if (B > MAX_GEMV_BATCH) return enqueue_wide_step(e, B, nsplit);
   const ModelDims& d = e->d;
   const int H = d.hidden, QD = d.qd(), I = d.inter;
   const bool pdl = e->use_pdl;
@@ -382,24 +424,26 @@ static int create_impl(llmc_engine* e, const llmc_config& c) {
     E_TRY(cudaMemcpy(e->rope_sin, hs.data(), hs.size() * 4, cudaMemcpyHostToDevice));
   }
   // ---- decode workspace
+  // WB: rows of the wide (GEMM) decode path, used when a call carries more than MAX_GEMV_BATCH sequences
+  const int WB = std::max(MB, std::min(e->max_slots, MAX_WIDE_BATCH));
   if (int rc = dalloc(e, &e->x, (size_t)MB * H)) return rc;
-  if (int rc = dalloc(e, &e->q, (size_t)MB * QD)) return rc;
-  if (int rc = dalloc(e, &e->attn, (size_t)MB * QD)) return rc;
+  if (int rc = dalloc(e, &e->q, (size_t)WB * QD)) return rc;
+  if (int rc = dalloc(e, &e->attn, (size_t)WB * QD)) return rc;
   if (int rc = dalloc(e, &e->act, (size_t)MB * I)) return rc;
-  if (int rc = dalloc(e, &e->logits, (size_t)MB * V)) return rc;
-  if (int rc = dalloc(e, &e->d_slots, MB)) return rc;
+  if (int rc = dalloc(e, &e->logits, (size_t)WB * V)) return rc;
+  if (int rc = dalloc(e, &e->d_slots, WB)) return rc;
   if (int rc = dalloc(e, &e->d_pslot, 1)) return rc;
   const int lmb = std::max(gemv_lmhead_blocks(V), gemv_mma_lmhead_blocks(V));
   if (int rc = dalloc(e, &e->part_val, (size_t)MB * lmb)) return rc;
   if (int rc = dalloc(e, &e->part_idx, (size_t)MB * lmb)) return rc;
   if (int rc = dalloc(e, &e->lm_counter, 1)) return rc;
-  if (int rc = dalloc(e, &e->attn_counters, (size_t)MB * d.kv_heads)) return rc;
-  if (int rc = dalloc(e, &e->attn_scratch, attn_decode_scratch_floats(MB, d.q_heads, ATTN_MAX_SPLIT, D))) return rc;
-  if (int rc = dalloc(e, &e->d_out_tokens, (size_t)MB * MAX_STEPS_PER_CALL)) return rc;
+  if (int rc = dalloc(e, &e->attn_counters, (size_t)WB * d.kv_heads)) return rc;
+  if (int rc = dalloc(e, &e->attn_scratch, attn_decode_scratch_floats(WB, d.q_heads, ATTN_MAX_SPLIT, D))) return rc;
+  if (int rc = dalloc(e, &e->d_out_tokens, (size_t)WB * MAX_STEPS_PER_CALL)) return rc;
   if (int rc = dalloc(e, &e->d_step_counter, 1)) return rc;
   if (int rc = dalloc(e, &e->d_dummy_counter, 1)) return rc;
   E_TRY(cudaMemsetAsync(e->lm_counter, 0, sizeof(unsigned), e->stream));
-  E_TRY(cudaMemsetAsync(e->attn_counters, 0, (size_t)MB * d.kv_heads * sizeof(unsigned), e->stream));
+  E_TRY(cudaMemsetAsync(e->attn_counters, 0, (size_t)WB * d.kv_heads * sizeof(unsigned), e->stream));
   E_TRY(cudaMemsetAsync(e->d_step_counter, 0, sizeof(int), e->stream));
   E_TRY(cudaMemsetAsync(e->d_dummy_counter, 0, sizeof(int), e->stream));
   // ---- one-kernel batch-1 decode
@@ -424,7 +468,7 @@ static int create_impl(llmc_engine* e, const llmc_config& c) {
     E_TRY(cudaMemsetAsync(e->mega_counters, 0, (size_t)d.kv_heads * sizeof(unsigned), e->stream));
   }
   // ---- prefill workspace
-  const int TC = e->prefill_chunk;
+  const int TC = std::max(e->prefill_chunk, WB);   // the wide decode path borrows these buffers (rows = sequences)
   if (int rc = dalloc(e, &e->p_tokens, TC)) return rc;
   if (int rc = dalloc(e, &e->px, (size_t)TC * H)) return rc;
   if (int rc = dalloc(e, &e->pxn, (size_t)TC * H)) return rc;
@@ -649,7 +693,7 @@ static int decode_group(llmc_engine* e, const int32_t* slots, int32_t nslots, in
   for (int st = 0; st < nsteps && !mega; ++st) {
     if (ge) {
       E_TRY(cudaGraphLaunch(ge, s));
-      e->stats.kernel_launches += (uint64_t)d.layers * 5 + 1;
+      e->stats.kernel_launches += nslots > MAX_GEMV_BATCH ? (uint64_t)d.layers * 9 + 4 : (uint64_t)d.layers * 5 + 1;
     } else {
       if (int rc = enqueue_decode_step(e, nslots, want_logits, nsplit)) return rc;
     }
@@ -710,12 +754,12 @@ int llmc_decode(llmc_engine* e, const int32_t* slots, int32_t nslots, int32_t ns
     if (e->h_seq_len[slots[i]] + nsteps > e->max_ctx)
       return fail(e, LLMC_ERR_LIMIT, "sequence would exceed max_ctx (" + std::to_string(e->max_ctx) + " tokens)");
   }
-  // The decode kernels batch up to 8 sequences against one pass over the weights; larger batches are
-  // run as consecutive groups of 8 (sequences are independent, so the order does not matter).  A
-  // tensor-core skinny GEMM that keeps batches of 16-128 on the HBM roof is future work.
+  // Up to 8 sequences: the GEMV kernels; 9..128: the wide path (tcgen05 skinny GEMMs), one pass over the
+  // weights for the whole group; more than 128 run as consecutive groups (sequences are independent).
   float total_ms = 0.f;
-  for (int g0 = 0; g0 < nslots; g0 += MAX_GEMV_BATCH) {
-    const int n = std::min<int>(MAX_GEMV_BATCH, nslots - g0);
+  const int group = nslots > MAX_GEMV_BATCH ? MAX_WIDE_BATCH : MAX_GEMV_BATCH;
+  for (int g0 = 0; g0 < nslots; g0 += group) {
+    const int n = std::min<int>(group, nslots - g0);
     int rc = decode_group(e, slots + g0, n, nsteps, out_tokens ? out_tokens + (size_t)g0 * nsteps : nullptr,
                           logits ? logits + (size_t)g0 * e->d.vocab : nullptr);
     if (rc != LLMC_OK) return rc;

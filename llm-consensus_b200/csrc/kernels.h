@@ -15,6 +15,7 @@ enum GemvPro { PRO_PLAIN = 0, PRO_NORM = 1, PRO_EMBED_NORM = 2 };
 enum GemvEpi { EPI_STORE = 0, EPI_RESID = 1, EPI_QKV_ROPE = 2, EPI_SWIGLU = 3, EPI_LMHEAD = 4 };
 
 constexpr int MAX_GEMV_BATCH = 8;
+constexpr int MAX_WIDE_BATCH = 128;  // sequences per pass over the weights on the wide (GEMM) decode path
 
 struct GemvArgs {
   // weights, packed [N][K] bf16, row-major, K % 256 == 0
@@ -152,6 +153,20 @@ cudaError_t launch_prefill_attention_mma(const float* q, int T, int p0, int slot
                                          int bt_stride, const void* kpool, const void* vpool, int kv_fp32,
                                          int page_size, int q_heads, int kv_heads, int head_dim, uint16_t* out_hi,
                                          uint16_t* out_lo, uint16_t* workspace, cudaStream_t s);
+
+// ------------------------------------------------------------------ decode_wide.cu (decode, 9..128 sequences)
+cudaError_t launch_embed_slots(const uint16_t* emb, const int* next_token, const int* slots, int B, int H, float* x,
+                               cudaStream_t s);
+cudaError_t launch_rope_append_batch(const float* qkv, int B, const int* slots, const int* seq_len,
+                                     const float* rope_cos, const float* rope_sin, const int* block_table,
+                                     int bt_stride, void* kpool, void* vpool, int kv_fp32, int page_size, int q_heads,
+                                     int kv_heads, int head_dim, float* q_out, cudaStream_t s);
+cudaError_t launch_split_rows(const float* x, size_t n, uint16_t* hi, uint16_t* lo, cudaStream_t s);
+// greedy argmax of B logit rows (lowest index on ties); writes next_token / seq_len (+1) / out_tokens[b][*step_counter]
+// and advances the step counter once per launch
+cudaError_t launch_argmax_finalise(const float* logits, int B, int V, const int* slots, int* next_token, int* seq_len,
+                                   int* out_tokens, int out_stride, int* step_counter, unsigned* ticket,
+                                   cudaStream_t s);
 
 // ------------------------------------------------------------------ gemm_tcgen05.cu / gemm_simple.cu (prefill)
 // C[T][N] = (A_hi [+ A_lo])[T][K] (bf16) * W[N][K]^T (bf16), fp32 accumulation.  A_lo may be NULL.

@@ -229,11 +229,11 @@ def test_chunked_prefill_equals_single_pass(gpu):
     e.close(); e2.close()
 
 
-@pytest.mark.parametrize("B", [2, 3, 5, 8, 11])
+@pytest.mark.parametrize("B", [2, 3, 5, 8, 11, 16, 33, 128, 131])   # <= 8: GEMV kernels; 9..128: wide (GEMM) path; > 128: groups
 def test_batched_decode_matches_per_sequence_oracle(gpu, B):
     name = "tiny"
     V = DIMS[name]["vocab"]
-    e = gpu.Engine(dims=DIMS[name], seed=4, max_ctx=256, max_slots=12, prefill_impl=DEFAULT_IMPL)
+    e = gpu.Engine(dims=DIMS[name], seed=4, max_ctx=256, max_slots=max(12, B), prefill_impl=DEFAULT_IMPL)
     rng = np.random.default_rng(B)
     prompts = [rng.integers(0, V, int(n)) for n in rng.integers(3, 90, B)]
     slots, firsts = [], []
@@ -243,8 +243,9 @@ def test_batched_decode_matches_per_sequence_oracle(gpu, B):
         firsts.append(e.prefill(s, p))
     n_new = 12
     out, lg = e.decode(slots, n_new, want_logits=True)
+    o = ref.Oracle(name, seed=4, max_ctx=256)
     for i, p in enumerate(prompts):
-        o = ref.Oracle(name, seed=4, max_ctx=256)
+        o.reset()
         otoks, olog = o.generate(p, n_new + 1, want_logits=True)
         gt = [firsts[i]] + out[i].tolist()
         where, margin = greedy_agreement(otoks, olog, gt)
