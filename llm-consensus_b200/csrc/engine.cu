@@ -159,8 +159,8 @@ int ensure_pages(llmc_engine* e, int slot, int need_tokens) {
 }
 
 int gemm(llmc_engine* e, const uint16_t* A, const uint16_t* Alo, const uint16_t* W, void* out, void* out_lo, int T,
-         int N, int K, int epi) {
-  if (e->prefill_impl == 0) E_TRY(launch_gemm_tcgen05(A, Alo, W, out, out_lo, T, N, K, epi, e->stream));
+         int N, int K, int epi, bool decode = false) {
+  if (e->prefill_impl == 0) E_TRY(launch_gemm_tcgen05(A, Alo, W, out, out_lo, T, N, K, epi, e->stream, decode));
   else E_TRY(launch_gemm_simple(A, Alo, W, out, out_lo, T, N, K, epi, e->stream));
   e->stats.kernel_launches++;
   return LLMC_OK;
@@ -219,7 +219,7 @@ int enqueue_wide_step(llmc_engine* e, int B, int nsplit) {
     unsigned char* kp = e->kpool + (size_t)l * e->kv_layer_stride * e->kv_elem;
     unsigned char* vp = e->vpool + (size_t)l * e->kv_layer_stride * e->kv_elem;
     E_TRY(launch_rmsnorm_rows(e->px, w.g1, d.rms_eps, B, H, e->pxn, e->pxn_lo, s));
-    if (int rc = gemm(e, e->pxn, e->pxn_lo, w.wqkv, e->pqkv, nullptr, B, QD + 2 * KD, H, GEMM_STORE_F32)) return rc;
+    if (int rc = gemm(e, e->pxn, e->pxn_lo, w.wqkv, e->pqkv, nullptr, B, QD + 2 * KD, H, GEMM_STORE_F32, true)) return rc;
     E_TRY(launch_rope_append_batch(e->pqkv, B, e->d_slots, e->d_seq_len, e->rope_cos, e->rope_sin, e->d_block_table,
                                    e->pages_per_seq, kp, vp, e->kv_fp32, e->page_size, d.q_heads, d.kv_heads,
                                    d.head_dim, e->q, s));
@@ -234,13 +234,13 @@ int enqueue_wide_step(llmc_engine* e, int B, int nsplit) {
       E_TRY(launch_attn_decode(a, false, s));
     }
     E_TRY(launch_split_rows(e->attn, (size_t)B * QD, e->pattn, e->pattn_lo, s));
-    if (int rc = gemm(e, e->pattn, e->pattn_lo, w.wo, e->px, nullptr, B, H, QD, GEMM_RESID_F32)) return rc;
+    if (int rc = gemm(e, e->pattn, e->pattn_lo, w.wo, e->px, nullptr, B, H, QD, GEMM_RESID_F32, true)) return rc;
     E_TRY(launch_rmsnorm_rows(e->px, w.g2, d.rms_eps, B, H, e->pxn, e->pxn_lo, s));
     if (int rc = gemm(e, e->pxn, e->pxn_lo, w.wgu, e->pact, e->pact_lo, B, 2 * I, H, GEMM_SWIGLU_BF16)) return rc;
-    if (int rc = gemm(e, e->pact, e->pact_lo, w.wd, e->px, nullptr, B, H, I, GEMM_RESID_F32)) return rc;
+    if (int rc = gemm(e, e->pact, e->pact_lo, w.wd, e->px, nullptr, B, H, I, GEMM_RESID_F32, true)) return rc;
   }
   E_TRY(launch_rmsnorm_rows(e->px, e->gf, d.rms_eps, B, H, e->pxn, e->pxn_lo, s));
-  if (int rc = gemm(e, e->pxn, e->pxn_lo, e->lmhead, e->logits, nullptr, B, V, H, GEMM_STORE_F32)) return rc;
+  if (int rc = gemm(e, e->pxn, e->pxn_lo, e->lmhead, e->logits, nullptr, B, V, H, GEMM_STORE_F32, true)) return rc;
   E_TRY(launch_argmax_finalise(e->logits, B, V, e->d_slots, e->d_next_token, e->d_seq_len, e->d_out_tokens,
                                MAX_STEPS_PER_CALL, e->d_step_counter, e->lm_counter, s));
   e->stats.kernel_launches += (uint64_t)d.layers * 5 + 3;   // the GEMMs count themselves

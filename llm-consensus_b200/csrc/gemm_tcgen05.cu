@@ -121,7 +121,10 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1)
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int n0 = blockIdx.x * BN, m0 = blockIdx.y * BM;
-  const int KB = K / BK;
+  // split-K (decode GEMMs, one M tile and few N tiles): gridDim.z CTAs share an output tile, each takes a
+  // contiguous range of k-blocks and adds its partial sum into the fp32 output with vector reductions
+  const int KB = K / BK / (int)gridDim.z;
+  const int kb0 = (int)blockIdx.z * KB;
 
   if (threadIdx.x == 0) {
     asm volatile("prefetch.tensormap [%0];" ::"l"(&tmA) : "memory");
@@ -153,9 +156,9 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1)
         mbar_wait(empty_bar(s), ph ^ 1u);
         mbar_expect_tx(full_bar(s), C::STAGE_BYTES);
         const uint32_t sa = base + s * C::STAGE_BYTES;
-        tma_load_2d(sa, &tmA, kb * BK, m0, full_bar(s));
-        if (SPLIT) tma_load_2d(sa + C::A_BYTES, &tmAlo, kb * BK, m0, full_bar(s));
-        tma_load_2d(sa + C::A_TILES * C::A_BYTES, &tmW, kb * BK, n0, full_bar(s));
+        tma_load_2d(sa, &tmA, (kb0 + kb) * BK, m0, full_bar(s));
+        if (SPLIT) tma_load_2d(sa + C::A_BYTES, &tmAlo, (kb0 + kb) * BK, m0, full_bar(s));
+        tma_load_2d(sa + C::A_TILES * C::A_BYTES, &tmW, (kb0 + kb) * BK, n0, full_bar(s));
       }
     }
   } else if (warp == 1) {
@@ -239,6 +242,15 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1)
             }
           } else {
             float4* dst = reinterpret_cast<float4*>(reinterpret_cast<float*>(out) + off);
+            if (gridDim.z > 1) {   // partial sum: out (zeroed by the launcher, or the residual) += acc
+#pragma unroll
+              for (int i = 0; i < 8; ++i)
+                asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(dst + i),
+                             "f"(__uint_as_float(v[4 * i])), "f"(__uint_as_float(v[4 * i + 1])),
+                             "f"(__uint_as_float(v[4 * i + 2])), "f"(__uint_as_float(v[4 * i + 3]))
+                             : "memory");
+              continue;
+            }
 #pragma unroll
             for (int i = 0; i < 8; ++i) {
               float4 r = make_float4(__uint_as_float(v[4 * i]), __uint_as_float(v[4 * i + 1]),
@@ -295,7 +307,7 @@ bool make_map(CUtensorMap* m, const void* ptr, uint64_t rows, uint64_t cols, uin
 
 template <int BN, int EPI, bool SPLIT>
 cudaError_t launch_tile(const uint16_t* A, const uint16_t* Alo, const uint16_t* W, void* out, void* out_lo, int T,
-                        int N, int K, cudaStream_t s) {
+                        int N, int K, cudaStream_t s, int ksplit = 1) {
   CUtensorMap ma, ml, mw;
   if (!make_map(&ma, A, (uint64_t)T, (uint64_t)K, BM) || !make_map(&mw, W, (uint64_t)N, (uint64_t)K, BN) ||
       !make_map(&ml, SPLIT ? Alo : A, (uint64_t)T, (uint64_t)K, BM))
@@ -303,16 +315,35 @@ cudaError_t launch_tile(const uint16_t* A, const uint16_t* Alo, const uint16_t* 
   auto kern = gemm_tc_kernel<BN, EPI, SPLIT>;
   cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, TileCfg<BN, SPLIT>::SMEM);
   if (e != cudaSuccess) return e;
-  dim3 grid(N / BN, (T + BM - 1) / BM);
+  dim3 grid(N / BN, (T + BM - 1) / BM, ksplit);
+  if (ksplit > 1 && EPI == GEMM_STORE_F32) {
+    e = cudaMemsetAsync(out, 0, (size_t)T * N * sizeof(float), s);
+    if (e != cudaSuccess) return e;
+  }
   kern<<<grid, GEMM_THREADS, TileCfg<BN, SPLIT>::SMEM, s>>>(ma, ml, mw, out, out_lo, T, N, K);
   return cudaGetLastError();
 }
 
+// largest power-of-two split of the k-blocks that keeps the grid within about one wave and >= 4 k-blocks per CTA
+int pick_ksplit(int tiles, int kblocks) {
+  int s = 1;
+  while (s < 32 && tiles * (s * 2) <= 160 && kblocks % (s * 2) == 0 && kblocks / (s * 2) >= 4) s *= 2;
+  return s;
+}
+
 template <int EPI, bool SPLIT>
 cudaError_t launch_epi(const uint16_t* A, const uint16_t* Alo, const uint16_t* W, void* out, void* out_lo, int T,
-                       int N, int K, cudaStream_t s) {
+                       int N, int K, cudaStream_t s, bool allow_ksplit) {
   // pick the widest tile that still yields at least ~one wave of CTAs on 148 SMs
   const int mt = (T + BM - 1) / BM;
+  if constexpr (EPI == GEMM_STORE_F32 || EPI == GEMM_RESID_F32) {
+    // decode-shaped call (one M tile): wide tiles + split-K instead of narrow tiles, so that the activations
+    // are re-read from L2 by few CTAs and every SM still has work
+    if (allow_ksplit && mt == 1 && N % 128 == 0 && N / 128 < 148) {
+      const int ks = pick_ksplit(N / 128, K / BK);
+      if (ks > 1) return launch_tile<128, EPI, SPLIT>(A, Alo, W, out, out_lo, T, N, K, s, ks);
+    }
+  }
   if (N % 256 == 0 && (N / 256) * mt >= 148) return launch_tile<256, EPI, SPLIT>(A, Alo, W, out, out_lo, T, N, K, s);
   if constexpr (EPI == GEMM_SWIGLU_BF16) {
     if (N % 128 != 0) return cudaErrorInvalidValue;
@@ -325,12 +356,12 @@ cudaError_t launch_epi(const uint16_t* A, const uint16_t* Alo, const uint16_t* W
 
 template <bool SPLIT>
 cudaError_t launch_split(const uint16_t* A, const uint16_t* Alo, const uint16_t* W, void* out, void* out_lo, int T,
-                         int N, int K, int epi, cudaStream_t s) {
+                         int N, int K, int epi, cudaStream_t s, bool ks) {
   switch (epi) {
-    case GEMM_STORE_BF16: return launch_epi<GEMM_STORE_BF16, SPLIT>(A, Alo, W, out, out_lo, T, N, K, s);
-    case GEMM_STORE_F32: return launch_epi<GEMM_STORE_F32, SPLIT>(A, Alo, W, out, out_lo, T, N, K, s);
-    case GEMM_RESID_F32: return launch_epi<GEMM_RESID_F32, SPLIT>(A, Alo, W, out, out_lo, T, N, K, s);
-    case GEMM_SWIGLU_BF16: return launch_epi<GEMM_SWIGLU_BF16, SPLIT>(A, Alo, W, out, out_lo, T, N, K, s);
+    case GEMM_STORE_BF16: return launch_epi<GEMM_STORE_BF16, SPLIT>(A, Alo, W, out, out_lo, T, N, K, s, ks);
+    case GEMM_STORE_F32: return launch_epi<GEMM_STORE_F32, SPLIT>(A, Alo, W, out, out_lo, T, N, K, s, ks);
+    case GEMM_RESID_F32: return launch_epi<GEMM_RESID_F32, SPLIT>(A, Alo, W, out, out_lo, T, N, K, s, ks);
+    case GEMM_SWIGLU_BF16: return launch_epi<GEMM_SWIGLU_BF16, SPLIT>(A, Alo, W, out, out_lo, T, N, K, s, ks);
   }
   return cudaErrorInvalidValue;
 }
@@ -338,10 +369,10 @@ cudaError_t launch_split(const uint16_t* A, const uint16_t* Alo, const uint16_t*
 }  // namespace
 
 cudaError_t launch_gemm_tcgen05(const uint16_t* A, const uint16_t* Alo, const uint16_t* W, void* out, void* out_lo,
-                                int T, int N, int K, int epi, cudaStream_t s) {
+                                int T, int N, int K, int epi, cudaStream_t s, bool allow_ksplit) {
   if (K % BK != 0 || T < 1 || N % 64 != 0) return cudaErrorInvalidValue;
-  return Alo ? launch_split<true>(A, Alo, W, out, out_lo, T, N, K, epi, s)
-             : launch_split<false>(A, Alo, W, out, out_lo, T, N, K, epi, s);
+  return Alo ? launch_split<true>(A, Alo, W, out, out_lo, T, N, K, epi, s, allow_ksplit)
+             : launch_split<false>(A, Alo, W, out, out_lo, T, N, K, epi, s, allow_ksplit);
 }
 
 }  // namespace llmc

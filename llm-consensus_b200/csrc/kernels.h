@@ -176,8 +176,10 @@ enum GemmEpi {
   GEMM_RESID_F32 = 2,   // out f32  [T][N] += acc
   GEMM_SWIGLU_BF16 = 3  // W rows gate/up interleaved in blocks of 64; out bf16 [T][N/2] = silu(g)*u (hi [, lo])
 };
+// allow_ksplit: decode-shaped calls (T <= 128, fp32 output) may split K over several CTAs per output tile, which add
+// their partial sums with fp32 reductions (summation order then varies from run to run in the last bits)
 cudaError_t launch_gemm_tcgen05(const uint16_t* A_hi, const uint16_t* A_lo, const uint16_t* W, void* out,
-                                void* out_lo, int T, int N, int K, int epi, cudaStream_t s);
+                                void* out_lo, int T, int N, int K, int epi, cudaStream_t s, bool allow_ksplit = false);
 cudaError_t launch_gemm_simple(const uint16_t* A_hi, const uint16_t* A_lo, const uint16_t* W, void* out,
                                void* out_lo, int T, int N, int K, int epi, cudaStream_t s);
 

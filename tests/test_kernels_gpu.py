@@ -203,6 +203,19 @@ def test_gemm_simple_comparator(gpu, T, N, K, epi, split):
     assert r.get("pair_max_excess", 0) <= 0, r
 
 
+# decode-shaped GEMMs (one M tile): impl 2 = tcgen05 with split-K allowed (partial sums added by fp32 reductions)
+SPLITK_CASES = [(128, 2048, 8192, 2), (17, 2048, 2048, 2), (64, 3072, 2048, 1), (128, 1024, 512, 1), (9, 4096, 4096, 2),
+                (100, 6144, 4096, 1)]
+
+
+@pytest.mark.parametrize("split", [0, 1])
+@pytest.mark.parametrize("T,N,K,epi", SPLITK_CASES)
+def test_gemm_tcgen05_split_k(gpu, T, N, K, epi, split):
+    r = run_gemm_check(T, N, K, epi, impl=2, split=split)
+    assert r["bad_rows"] == 0, r
+    assert r["max_excess"] <= 0, r
+
+
 @pytest.mark.parametrize("split", [0, 1])
 @pytest.mark.parametrize("T,N,K,epi", GEMM_CASES)
 def test_gemm_tcgen05(gpu, T, N, K, epi, split):
