@@ -44,7 +44,8 @@ int llmc_op_attn_decode(int device, int B, int q_heads, int kv_heads, int head_d
                         float* out);
 
 /* Prefill GEMM C = (A + A_lo) W^T.  A_lo may be NULL (single bf16 operand).  impl 0: tcgen05;
- * 1: plain CUDA-core comparator; 2: tcgen05 with split-K allowed (the wide-batch decode calls).  epi: 0 bf16 store, 1 f32 store, 2 f32 residual add (out is
+ * 1: plain CUDA-core comparator; 2: tcgen05 with split-K allowed;
+ * 3: the decode kernel (operands swapped: weights as the M tile, T <= 128; epi 1, 2, 3 only).  epi: 0 bf16 store, 1 f32 store, 2 f32 residual add (out is
  * in/out), 3 SwiGLU on logical Wg|Wu given as W = [Wg ; Wu] ([2I][K], packed inside), out bf16
  * [T][I] with the optional low half in out_lo (NULL otherwise). */
 int llmc_op_gemm(int device, int impl, int epi, int T, int N, int K, const uint16_t* A, const uint16_t* A_lo,

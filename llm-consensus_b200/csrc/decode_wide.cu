@@ -91,19 +91,22 @@ __global__ void __launch_bounds__(256) split_rows_kernel(const float* __restrict
   }
 }
 
-// one block per row; the last block to finish (ticket) advances the step counter
-__global__ void __launch_bounds__(1024) argmax_finalise_kernel(const float* __restrict__ logits, int V,
-                                                               const int* __restrict__ slots, int* __restrict__ next_token,
-                                                               int* __restrict__ seq_len, int* __restrict__ out_tokens,
-                                                               int out_stride, int* __restrict__ step_counter,
-                                                               unsigned* __restrict__ ticket) {
-  __shared__ float s_val[32];
-  __shared__ int s_idx[32];
-  const int b = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+// Greedy argmax in two stages.  Stage 1: grid (chunks, B), each block scans one chunk of a row and leaves a
+// (value, index) candidate.  Stage 2: one warp per row reduces the candidates (lowest index on ties), writes
+// next_token / seq_len / the output token; the last row to finish (ticket) advances the step counter.
+constexpr int AM_CHUNKS = 32;
+
+__global__ void __launch_bounds__(256) argmax_partial_kernel(const float* __restrict__ logits, int V,
+                                                             float* __restrict__ part_val, int* __restrict__ part_idx) {
+  __shared__ float s_val[8];
+  __shared__ int s_idx[8];
+  const int chunk = blockIdx.x, b = blockIdx.y, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int per = (V + AM_CHUNKS - 1) / AM_CHUNKS;
+  const int lo = chunk * per, hi = min(V, lo + per);
   const float* row = logits + (size_t)b * V;
   float best = -INFINITY;
   int bi = 0x7fffffff;
-  for (int i = tid; i < V; i += blockDim.x) {   // ascending i per thread: strict > keeps the lowest index
+  for (int i = lo + tid; i < hi; i += 256) {   // ascending i per thread: strict > keeps the lowest index
     const float v = row[i];
     if (v > best) { best = v; bi = i; }
   }
@@ -115,27 +118,40 @@ __global__ void __launch_bounds__(1024) argmax_finalise_kernel(const float* __re
   }
   if (lane == 0) { s_val[warp] = best; s_idx[warp] = bi; }
   __syncthreads();
-  if (warp == 0) {
-    const int nw = blockDim.x >> 5;
-    best = lane < nw ? s_val[lane] : -INFINITY;
-    bi = lane < nw ? s_idx[lane] : 0x7fffffff;
+  if (tid == 0) {
 #pragma unroll
-    for (int o = 16; o > 0; o >>= 1) {
-      const float ov = __shfl_xor_sync(0xffffffffu, best, o);
-      const int oi = __shfl_xor_sync(0xffffffffu, bi, o);
-      if (ov > best || (ov == best && oi < bi)) { best = ov; bi = oi; }
-    }
-    if (lane == 0) {
-      const int slot = slots[b];
-      const int step = *step_counter;
-      next_token[slot] = bi;
-      seq_len[slot] += 1;
-      out_tokens[(size_t)b * out_stride + step] = bi;
-      __threadfence();
-      if (atomicAdd(ticket, 1u) == gridDim.x - 1) {   // every block has read the counter
-        *step_counter = step + 1;
-        *ticket = 0u;
-      }
+    for (int w = 1; w < 8; ++w)
+      if (s_val[w] > best || (s_val[w] == best && s_idx[w] < bi)) { best = s_val[w]; bi = s_idx[w]; }
+    part_val[b * AM_CHUNKS + chunk] = best;
+    part_idx[b * AM_CHUNKS + chunk] = bi;
+  }
+}
+
+__global__ void __launch_bounds__(32) argmax_finalise_kernel(const float* __restrict__ part_val,
+                                                             const int* __restrict__ part_idx,
+                                                             const int* __restrict__ slots, int* __restrict__ next_token,
+                                                             int* __restrict__ seq_len, int* __restrict__ out_tokens,
+                                                             int out_stride, int* __restrict__ step_counter,
+                                                             unsigned* __restrict__ ticket) {
+  const int b = blockIdx.x, lane = threadIdx.x;
+  float best = part_val[b * AM_CHUNKS + lane];
+  int bi = part_idx[b * AM_CHUNKS + lane];
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    const float ov = __shfl_xor_sync(0xffffffffu, best, o);
+    const int oi = __shfl_xor_sync(0xffffffffu, bi, o);
+    if (ov > best || (ov == best && oi < bi)) { best = ov; bi = oi; }
+  }
+  if (lane == 0) {
+    const int slot = slots[b];
+    const int step = *step_counter;
+    next_token[slot] = bi;
+    seq_len[slot] += 1;
+    out_tokens[(size_t)b * out_stride + step] = bi;
+    __threadfence();
+    if (atomicAdd(ticket, 1u) == gridDim.x - 1) {   // every row has read the counter
+      *step_counter = step + 1;
+      *ticket = 0u;
     }
   }
 }
@@ -167,11 +183,17 @@ cudaError_t launch_split_rows(const float* x, size_t n, uint16_t* hi, uint16_t* 
   return cudaGetLastError();
 }
 
+size_t argmax_scratch_elems(int B) { return (size_t)B * AM_CHUNKS; }
+
 cudaError_t launch_argmax_finalise(const float* logits, int B, int V, const int* slots, int* next_token, int* seq_len,
                                    int* out_tokens, int out_stride, int* step_counter, unsigned* ticket,
-                                   cudaStream_t s) {
-  argmax_finalise_kernel<<<B, 1024, 0, s>>>(logits, V, slots, next_token, seq_len, out_tokens, out_stride,
-                                             step_counter, ticket);
+                                   float* part_val, int* part_idx, cudaStream_t s) {
+  static_assert(AM_CHUNKS == 32, "stage 2 reduces one candidate per lane");
+  argmax_partial_kernel<<<dim3(AM_CHUNKS, B), 256, 0, s>>>(logits, V, part_val, part_idx);
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) return e;
+  argmax_finalise_kernel<<<B, 32, 0, s>>>(part_val, part_idx, slots, next_token, seq_len, out_tokens, out_stride,
+                                           step_counter, ticket);
   return cudaGetLastError();
 }
 

@@ -160,7 +160,10 @@ int ensure_pages(llmc_engine* e, int slot, int need_tokens) {
 
 int gemm(llmc_engine* e, const uint16_t* A, const uint16_t* Alo, const uint16_t* W, void* out, void* out_lo, int T,
          int N, int K, int epi, bool decode = false) {
-  if (e->prefill_impl == 0) E_TRY(launch_gemm_tcgen05(A, Alo, W, out, out_lo, T, N, K, epi, e->stream, decode));
+  // up to 32 rows the swapped-operand decode kernel wins (deeper weight pipeline); above, the prefill kernel + split-K
+  if (e->prefill_impl == 0 && decode && T <= 32 && gemm_decode_tc_supported(T, N, K, epi))
+    E_TRY(launch_gemm_decode_tc(A, Alo, W, out, out_lo, T, N, K, epi, e->stream));
+  else if (e->prefill_impl == 0) E_TRY(launch_gemm_tcgen05(A, Alo, W, out, out_lo, T, N, K, epi, e->stream, decode));
   else E_TRY(launch_gemm_simple(A, Alo, W, out, out_lo, T, N, K, epi, e->stream));
   e->stats.kernel_launches++;
   return LLMC_OK;
@@ -236,20 +239,20 @@ int enqueue_wide_step(llmc_engine* e, int B, int nsplit) {
     E_TRY(launch_split_rows(e->attn, (size_t)B * QD, e->pattn, e->pattn_lo, s));
     if (int rc = gemm(e, e->pattn, e->pattn_lo, w.wo, e->px, nullptr, B, H, QD, GEMM_RESID_F32, true)) return rc;
     E_TRY(launch_rmsnorm_rows(e->px, w.g2, d.rms_eps, B, H, e->pxn, e->pxn_lo, s));
-    if (int rc = gemm(e, e->pxn, e->pxn_lo, w.wgu, e->pact, e->pact_lo, B, 2 * I, H, GEMM_SWIGLU_BF16)) return rc;
+    if (int rc = gemm(e, e->pxn, e->pxn_lo, w.wgu, e->pact, e->pact_lo, B, 2 * I, H, GEMM_SWIGLU_BF16, true)) return rc;
     if (int rc = gemm(e, e->pact, e->pact_lo, w.wd, e->px, nullptr, B, H, I, GEMM_RESID_F32, true)) return rc;
   }
   E_TRY(launch_rmsnorm_rows(e->px, e->gf, d.rms_eps, B, H, e->pxn, e->pxn_lo, s));
   if (int rc = gemm(e, e->pxn, e->pxn_lo, e->lmhead, e->logits, nullptr, B, V, H, GEMM_STORE_F32, true)) return rc;
   E_TRY(launch_argmax_finalise(e->logits, B, V, e->d_slots, e->d_next_token, e->d_seq_len, e->d_out_tokens,
-                               MAX_STEPS_PER_CALL, e->d_step_counter, e->lm_counter, s));
-  e->stats.kernel_launches += (uint64_t)d.layers * 5 + 3;   // the GEMMs count themselves
+                               MAX_STEPS_PER_CALL, e->d_step_counter, e->lm_counter, e->part_val, e->part_idx, s));
+  e->stats.kernel_launches += (uint64_t)d.layers * 5 + 4;   // the GEMMs count themselves
   return LLMC_OK;
 }
 
 // enqueue one decode step for the B sequences listed in d_slots
 int enqueue_decode_step(llmc_engine* e, int B, bool want_logits, int nsplit) {
-  if (B > MAX_GEMV_BATCH) return enqueue_wide_step(e, B, nsplit);
+  if (B >= e->wide_min_batch) return enqueue_wide_step(e, B, nsplit);
   const ModelDims& d = e->d;
   const int H = d.hidden, QD = d.qd(), I = d.inter;
   const bool pdl = e->use_pdl;
@@ -379,6 +382,11 @@ static int create_impl(llmc_engine* e, const llmc_config& c) {
   e->kv_elem = e->kv_fp32 ? 4 : 2;
   e->split_prefill = !(c.flags & LLMC_FLAG_PREFILL_BF16);
   e->use_mega = !(c.flags & LLMC_FLAG_NO_MEGAKERNEL);
+  {
+    const char* wm = getenv("LLMC_WIDE_MIN_BATCH");   // experiment knob: smallest batch served by the wide (GEMM) decode path
+    e->wide_min_batch = wm ? std::max(2, atoi(wm)) : 4;
+    if (e->wide_min_batch > MAX_GEMV_BATCH + 1) e->wide_min_batch = MAX_GEMV_BATCH + 1;
+  }
   e->use_ring = e->use_mega && !(c.flags & LLMC_FLAG_NO_RING) &&
                 decode_ring_supported(e->d.hidden, e->d.qd(), e->d.kd(), e->d.inter, e->d.vocab, e->d.q_heads, e->d.kv_heads,
                                       e->d.head_dim);
@@ -434,8 +442,9 @@ static int create_impl(llmc_engine* e, const llmc_config& c) {
   if (int rc = dalloc(e, &e->d_slots, WB)) return rc;
   if (int rc = dalloc(e, &e->d_pslot, 1)) return rc;
   const int lmb = std::max(gemv_lmhead_blocks(V), gemv_mma_lmhead_blocks(V));
-  if (int rc = dalloc(e, &e->part_val, (size_t)MB * lmb)) return rc;
-  if (int rc = dalloc(e, &e->part_idx, (size_t)MB * lmb)) return rc;
+  const size_t npart = std::max((size_t)MB * lmb, argmax_scratch_elems(WB));
+  if (int rc = dalloc(e, &e->part_val, npart)) return rc;
+  if (int rc = dalloc(e, &e->part_idx, npart)) return rc;
   if (int rc = dalloc(e, &e->lm_counter, 1)) return rc;
   if (int rc = dalloc(e, &e->attn_counters, (size_t)WB * d.kv_heads)) return rc;
   if (int rc = dalloc(e, &e->attn_scratch, attn_decode_scratch_floats(WB, d.q_heads, ATTN_MAX_SPLIT, D))) return rc;
@@ -693,7 +702,7 @@ static int decode_group(llmc_engine* e, const int32_t* slots, int32_t nslots, in
   for (int st = 0; st < nsteps && !mega; ++st) {
     if (ge) {
       E_TRY(cudaGraphLaunch(ge, s));
-      e->stats.kernel_launches += nslots > MAX_GEMV_BATCH ? (uint64_t)d.layers * 9 + 4 : (uint64_t)d.layers * 5 + 1;
+      e->stats.kernel_launches += nslots >= e->wide_min_batch ? (uint64_t)d.layers * 9 + 5 : (uint64_t)d.layers * 5 + 1;
     } else {
       if (int rc = enqueue_decode_step(e, nslots, want_logits, nsplit)) return rc;
     }
@@ -757,7 +766,7 @@ int llmc_decode(llmc_engine* e, const int32_t* slots, int32_t nslots, int32_t ns
   // Up to 8 sequences: the GEMV kernels; 9..128: the wide path (tcgen05 skinny GEMMs), one pass over the
   // weights for the whole group; more than 128 run as consecutive groups (sequences are independent).
   float total_ms = 0.f;
-  const int group = nslots > MAX_GEMV_BATCH ? MAX_WIDE_BATCH : MAX_GEMV_BATCH;
+  const int group = nslots >= e->wide_min_batch ? MAX_WIDE_BATCH : MAX_GEMV_BATCH;
   for (int g0 = 0; g0 < nslots; g0 += group) {
     const int n = std::min<int>(group, nslots - g0);
     int rc = decode_group(e, slots + g0, n, nsteps, out_tokens ? out_tokens + (size_t)g0 * nsteps : nullptr,

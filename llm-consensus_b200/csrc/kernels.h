@@ -164,9 +164,10 @@ cudaError_t launch_rope_append_batch(const float* qkv, int B, const int* slots, 
 cudaError_t launch_split_rows(const float* x, size_t n, uint16_t* hi, uint16_t* lo, cudaStream_t s);
 // greedy argmax of B logit rows (lowest index on ties); writes next_token / seq_len (+1) / out_tokens[b][*step_counter]
 // and advances the step counter once per launch
+size_t argmax_scratch_elems(int B);   // part_val / part_idx sizes
 cudaError_t launch_argmax_finalise(const float* logits, int B, int V, const int* slots, int* next_token, int* seq_len,
                                    int* out_tokens, int out_stride, int* step_counter, unsigned* ticket,
-                                   cudaStream_t s);
+                                   float* part_val, int* part_idx, cudaStream_t s);
 
 // ------------------------------------------------------------------ gemm_tcgen05.cu / gemm_simple.cu (prefill)
 // C[T][N] = (A_hi [+ A_lo])[T][K] (bf16) * W[N][K]^T (bf16), fp32 accumulation.  A_lo may be NULL.
@@ -180,6 +181,12 @@ enum GemmEpi {
 // their partial sums with fp32 reductions (summation order then varies from run to run in the last bits)
 cudaError_t launch_gemm_tcgen05(const uint16_t* A_hi, const uint16_t* A_lo, const uint16_t* W, void* out,
                                 void* out_lo, int T, int N, int K, int epi, cudaStream_t s, bool allow_ksplit = false);
+// ------------------------------------------------------------------ gemm_decode_tc.cu (decode, <= 128 sequences)
+// Same product with the operands swapped on the tensor cores (weights = M tile, batch = N): out[B][N] fp32 store /
+// residual add / SwiGLU (bf16 hi [, lo]); split-K where a matrix has few row tiles.
+bool gemm_decode_tc_supported(int B, int N, int K, int epi);
+cudaError_t launch_gemm_decode_tc(const uint16_t* A_hi, const uint16_t* A_lo, const uint16_t* W, void* out,
+                                  void* out_lo, int B, int N, int K, int epi, cudaStream_t s);
 cudaError_t launch_gemm_simple(const uint16_t* A_hi, const uint16_t* A_lo, const uint16_t* W, void* out,
                                void* out_lo, int T, int N, int K, int epi, cudaStream_t s);
 

@@ -259,7 +259,8 @@ int llmc_op_gemm(int device, int impl, int epi, int T, int N, int K, const uint1
   O_TRY(pool.get(&dW, (size_t)N * K, hw));
   O_TRY(pool.get(&dout, out_bytes, epi == GEMM_RESID_F32 ? out : nullptr));
   if (out_lo && epi == GEMM_SWIGLU_BF16) O_TRY(pool.get(&dol, out_bytes));
-  if (impl == 0 || impl == 2) O_TRY(launch_gemm_tcgen05(dA, dAl, dW, dout, dol, T, N, K, epi, 0, impl == 2));
+  if (impl == 3) O_TRY(launch_gemm_decode_tc(dA, dAl, dW, dout, dol, T, N, K, epi, 0));
+  else if (impl == 0 || impl == 2) O_TRY(launch_gemm_tcgen05(dA, dAl, dW, dout, dol, T, N, K, epi, 0, impl == 2));
   else O_TRY(launch_gemm_simple(dA, dAl, dW, dout, dol, T, N, K, epi, 0));
   O_TRY(cudaDeviceSynchronize());
   O_TRY(cudaMemcpy(out, dout, out_bytes, cudaMemcpyDeviceToHost));
@@ -287,6 +288,7 @@ int llmc_op_gemm_bench(int device, int impl, int epi, int split, int T, int N, i
   O_TRY(cudaEventCreate(&e0));
   O_TRY(cudaEventCreate(&e1));
   auto run = [&]() {
+    if (impl == 3) return launch_gemm_decode_tc(dA, dAl, dW, dout, dol, T, N, K, epi, 0);
     return (impl == 0 || impl == 2) ? launch_gemm_tcgen05(dA, dAl, dW, dout, dol, T, N, K, epi, 0, impl == 2)
                      : launch_gemm_simple(dA, dAl, dW, dout, dol, T, N, K, epi, 0);
   };

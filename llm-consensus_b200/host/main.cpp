@@ -33,7 +33,7 @@ host::Context g_root = host::Context::Background();
 struct Config {
   std::vector<std::string> models;
   std::string judge = kDefaultJudge, file, output, dataDir = "data", prompt, weights;
-  int timeout = 120, device = 0, maxNew = 256;
+  int timeout = 120, device = 0, maxNew = 256, maxCtx = 8192;
   uint64_t seed = 0;
   bool quiet = false, json = false, noSave = false, version = false;
   std::vector<std::string> stubs;  // NAME=PROVIDER:DELAY_MS:CONTENT  (test stand-ins for remote providers)
@@ -110,6 +110,7 @@ Error parseFlags(int argc, char** argv, Config* cfg) {
     else if (name == "timeout") { e = integer(&n); cfg->timeout = (int)n; }
     else if (name == "device") { e = integer(&n); cfg->device = (int)n; }
     else if (name == "max-new-tokens") { e = integer(&n); cfg->maxNew = (int)n; }
+    else if (name == "max-ctx") { e = integer(&n); cfg->maxCtx = (int)n; }
     else if (name == "seed") { e = integer(&n); cfg->seed = (uint64_t)n; }
     else e = Error::New("flag provided but not defined: -" + name);
     if (e) return e;
@@ -213,6 +214,7 @@ Error createProvider(const std::string& model, const Config& cfg, int* next_devi
       lc.device = ndev > 0 ? (cfg.device + (*next_device)++) % ndev : cfg.device;  // one instance per GPU, round robin
       lc.weights_path = cfg.weights;
       lc.max_new_tokens = cfg.maxNew;
+      lc.max_ctx = cfg.maxCtx;
       return NewLocal(lc, out);
     }
   }
@@ -265,17 +267,35 @@ Error run(int argc, char** argv) {
     printf("llm-consensus dev (B200 local provider, %s)\n  commit: none\n  built:  unknown\n", llmc_version());
     return Error::Nil();
   }
+  using clk = std::chrono::steady_clock;
+  auto ms_since = [](clk::time_point t0) { return std::chrono::duration<double, std::milli>(clk::now() - t0).count(); };
+  // LLMC_BENCH_REPEAT=N (measurement aid, not a reference flag): run the fan-out + judge N times on the same
+  // providers and report each pass on stderr; the output written is the last pass's
+  const char* rep_env = getenv("LLMC_BENCH_REPEAT");
+  const int repeat = rep_env ? std::max(1, atoi(rep_env)) : 1;
+  const auto t_init = clk::now();
   Registry registry;
   if (Error e = initRegistry(cfg, &registry)) return e;
+  if (rep_env) fprintf(stderr, "[bench] providers ready in %.1f ms\n", ms_since(t_init));
   Runner r(&registry, std::chrono::seconds(cfg.timeout));
   RunResult result;
-  if (Error e = r.Run(g_root, cfg.models, cfg.prompt, &result)) return Error::New("running queries: " + e.msg);
-  std::shared_ptr<Provider> judgeProvider;
-  if (Error e = registry.Get(cfg.judge, &judgeProvider)) return Error::New("judge model " + cfg.judge + ": " + e.msg);
-  Judge judge(judgeProvider, cfg.judge);
   std::string consensus;
-  if (Error e = judge.SynthesizeStream(g_root, cfg.prompt, result.Responses, nullptr, &consensus))
-    return Error::New("consensus synthesis: " + e.msg);
+  for (int pass = 0; pass < repeat; ++pass) {
+    result = RunResult();
+    consensus.clear();
+    const auto t0 = clk::now();
+    if (Error e = r.Run(g_root, cfg.models, cfg.prompt, &result)) return Error::New("running queries: " + e.msg);
+    const double fan_ms = ms_since(t0);
+    std::shared_ptr<Provider> judgeProvider;
+    if (Error e = registry.Get(cfg.judge, &judgeProvider)) return Error::New("judge model " + cfg.judge + ": " + e.msg);
+    Judge judge(judgeProvider, cfg.judge);
+    const auto t1 = clk::now();
+    if (Error e = judge.SynthesizeStream(g_root, cfg.prompt, result.Responses, nullptr, &consensus))
+      return Error::New("consensus synthesis: " + e.msg);
+    if (rep_env)
+      fprintf(stderr, "[bench] pass %d: fan-out %.1f ms (%zu responses, %zu failed), judge %.1f ms, run %.1f ms\n", pass,
+              fan_ms, result.Responses.size(), result.FailedModels.size(), ms_since(t1), ms_since(t0));
+  }
   OutputResult out;
   out.Prompt = cfg.prompt;
   out.Responses = result.Responses;

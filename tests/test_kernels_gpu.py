@@ -216,6 +216,20 @@ def test_gemm_tcgen05_split_k(gpu, T, N, K, epi, split):
     assert r["max_excess"] <= 0, r
 
 
+# the decode GEMM (impl 3: weights as the M tile, the batch as N = 16/32/64/128)
+DECODE_GEMM_CASES = SPLITK_CASES + [(1, 256, 128, 1), (16, 16384, 2048, 3), (5, 1024, 512, 3), (33, 2048, 256, 3),
+                                    (128, 4096, 2048, 3), (70, 128256, 2048, 1), (40, 512, 14336, 2)]
+
+
+@pytest.mark.parametrize("split", [0, 1])
+@pytest.mark.parametrize("T,N,K,epi", DECODE_GEMM_CASES)
+def test_gemm_decode_tc(gpu, T, N, K, epi, split):
+    r = run_gemm_check(T, N, K, epi, impl=3, split=split, timeout=300)
+    assert r["bad_rows"] == 0, r
+    assert r["max_excess"] <= 0, r
+    assert r.get("pair_max_excess", 0) <= 0, r
+
+
 @pytest.mark.parametrize("split", [0, 1])
 @pytest.mark.parametrize("T,N,K,epi", GEMM_CASES)
 def test_gemm_tcgen05(gpu, T, N, K, epi, split):
