@@ -58,7 +58,8 @@ typedef struct llmc_config {
   float rms_eps;        /* 0 -> 1e-5 */
   float init_std;       /* 0 -> 0.02; weights are bf16(std*sqrt(3)*u), u from the counter RNG */
   uint64_t seed;        /* weight seed (the provider's --seed) */
-  const char* weights_path; /* NULL: random init from `seed` (the only mode implemented) */
+  const char* weights_path; /* NULL: random init from `seed`.  Else a .safetensors file or a directory of shards with
+                             * Hugging Face Llama tensor names (BF16 / F16 / F32; rounded to bf16), matching the shape. */
   int32_t max_slots;    /* concurrent sequences (0 -> 8) */
   int32_t max_ctx;      /* tokens per sequence (0 -> 8192) */
   int32_t page_size;    /* KV page, tokens; multiple of 32 (0 -> 64) */

@@ -89,11 +89,10 @@ std::string validate(const llmc_config& c) {
   if (c.max_ctx < 32) return "max_ctx < 32";
   if (c.prefill_chunk < 32) return "prefill_chunk < 32";
   if (c.prefill_impl != 0 && c.prefill_impl != 1) return "prefill_impl must be 0 or 1";
-  if (c.weights_path) return "weights_path: loading checkpoints is not implemented; pass NULL for seeded random init";
   return "";
 }
 
-int init_weights(llmc_engine* e) {
+int init_weights(llmc_engine* e, const char* weights_path) {
   const ModelDims& d = e->d;
   const int H = d.hidden, QD = d.qd(), KD = d.kd(), I = d.inter, V = d.vocab;
   const size_t per_layer = (size_t)2 * H + (size_t)(QD + 2 * KD) * H + (size_t)H * QD + (size_t)2 * I * H + (size_t)H * I;
@@ -114,6 +113,7 @@ int init_weights(llmc_engine* e) {
     w.wd = take((size_t)H * I);
     w.g1 = take(H);
     w.g2 = take(H);
+    if (weights_path) continue;   // layout only; filled from the checkpoint below
     E_TRY(launch_init_gain(w.g1, H, e->seed, tensor_id(l, K_ATTN_NORM), s));
     E_TRY(launch_init_matrix(w.wqkv, QD, H, H, e->seed, tensor_id(l, K_WQ), amp, 0, 0, s));
     E_TRY(launch_init_matrix(w.wqkv, KD, H, H, e->seed, tensor_id(l, K_WK), amp, 0, QD, s));
@@ -125,16 +125,21 @@ int init_weights(llmc_engine* e) {
     E_TRY(launch_init_matrix(w.wd, H, I, I, e->seed, tensor_id(l, K_WD), amp, 0, 0, s));
   }
   e->emb = take((size_t)V * H);
-  E_TRY(launch_init_matrix(e->emb, V, H, H, e->seed, tensor_id(-1, K_EMB), amp, 0, 0, s));
+  if (!weights_path) E_TRY(launch_init_matrix(e->emb, V, H, H, e->seed, tensor_id(-1, K_EMB), amp, 0, 0, s));
   if (d.tied) {
     e->lmhead = e->emb;
   } else {
     e->lmhead = take((size_t)V * H);
-    E_TRY(launch_init_matrix(e->lmhead, V, H, H, e->seed, tensor_id(-1, K_LMHEAD), amp, 0, 0, s));
+    if (!weights_path) E_TRY(launch_init_matrix(e->lmhead, V, H, H, e->seed, tensor_id(-1, K_LMHEAD), amp, 0, 0, s));
   }
   e->gf = take(H);
-  E_TRY(launch_init_gain(e->gf, H, e->seed, tensor_id(-1, K_FINAL_NORM), s));
-  e->stats.kernel_launches += (uint64_t)d.layers * 9 + 3;
+  if (!weights_path) E_TRY(launch_init_gain(e->gf, H, e->seed, tensor_id(-1, K_FINAL_NORM), s));
+  if (weights_path) {
+    std::string err;
+    if (int rc = load_checkpoint(e, weights_path, &err)) return fail(e, rc, "weights_path: " + err);
+  } else {
+    e->stats.kernel_launches += (uint64_t)d.layers * 9 + 3;
+  }
   e->stats.weight_bytes = 2.0 * ((double)per_layer * d.layers + (double)V * H + H);
   e->stats.kv_bytes_per_token = 2.0 * e->kv_elem * KD * d.layers;
   return LLMC_OK;
@@ -394,7 +399,7 @@ static int create_impl(llmc_engine* e, const llmc_config& c) {
   E_TRY(cudaStreamCreateWithFlags(&e->stream, cudaStreamNonBlocking));
   E_TRY(cudaEventCreate(&e->ev0));
   E_TRY(cudaEventCreate(&e->ev1));
-  if (int rc = init_weights(e)) return rc;
+  if (int rc = init_weights(e, c.weights_path)) return rc;
 
   const ModelDims& d = e->d;
   const int H = d.hidden, QD = d.qd(), KD = d.kd(), I = d.inter, V = d.vocab, D = d.head_dim;

@@ -16,6 +16,12 @@ struct LayerW {
 };
 }  // namespace llmc
 
+struct llmc_engine;
+namespace llmc {
+// checkpoint.cu: fill the (already laid out) weight blob from a safetensors file or directory of shards
+int load_checkpoint(llmc_engine* e, const char* path, std::string* err);
+}  // namespace llmc
+
 struct llmc_engine {
   int device = 0;
   llmc::ModelDims d{};

@@ -106,10 +106,12 @@ class Engine:
     """One model instance on one GPU (llmc_engine)."""
 
     def __init__(self, shape=SHAPE_LLAMA_1B, device=0, seed=0, max_slots=8, max_ctx=8192, page_size=64,
-                 prefill_chunk=2048, prefill_impl=0, flags=0, dims=None, rope_theta=0.0, rms_eps=0.0, init_std=0.0):
+                 prefill_chunk=2048, prefill_impl=0, flags=0, dims=None, rope_theta=0.0, rms_eps=0.0, init_std=0.0,
+                 weights_path=None):
         cfg = Config(device=device, shape=shape, seed=seed, max_slots=max_slots, max_ctx=max_ctx,
                      page_size=page_size, prefill_chunk=prefill_chunk, prefill_impl=prefill_impl, flags=flags,
-                     rope_theta=rope_theta, rms_eps=rms_eps, init_std=init_std, weights_path=None)
+                     rope_theta=rope_theta, rms_eps=rms_eps, init_std=init_std,
+                     weights_path=weights_path.encode() if weights_path else None)
         if dims:
             cfg.shape = SHAPE_CUSTOM
             for k, v in dims.items():
