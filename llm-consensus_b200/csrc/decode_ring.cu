@@ -386,6 +386,7 @@ __global__ void __launch_bounds__(RTHREADS, 1) decode_ring_kernel(const MegaArgs
       const MegaLayer& ly = a.layers[l];
       KVT* kpool = reinterpret_cast<KVT*>(ly.kp);
       KVT* vpool = reinterpret_cast<KVT*>(ly.vp);
+      const int nsp = min(RING_MAX_SPLIT, max(1, (ntiles + a.attn_tiles_per_block - 1) / a.attn_tiles_per_block));
 
       // ---------------- P1: RMSNorm -> QKV -> RoPE -> KV append
       {
@@ -421,11 +422,28 @@ __global__ void __launch_bounds__(RTHREADS, 1) decode_ring_kernel(const MegaArgs
             }
           }
         });
+        // The K/V tiles this block's warps will read in the attention phase were written by earlier steps (only the
+        // newest row is from this one) and have long been evicted from L2 by the weight stream: ask L2 for them now,
+        // so the two dependent tile loads (K, then V) of the attention phase cost an L2 trip instead of an HBM trip.
+        if ((int)blockIdx.x < a.kv_heads * nsp) {
+          const int kvh = blockIdx.x % a.kv_heads, split = blockIdx.x / a.kv_heads;
+          constexpr int TILE_LINES = TP * D * (int)sizeof(KVT) / 128;
+          for (int tile = split + nsp * warp; tile < ntiles; tile += nsp * RW) {
+            const int p0 = tile * TP;
+            const int page = bt[p0 / a.page_size];
+            const size_t base = (((size_t)page * a.kv_heads + kvh) * a.page_size + (p0 % a.page_size)) * D;
+            const char* kb = reinterpret_cast<const char*>(kpool + base);
+            const char* vb = reinterpret_cast<const char*>(vpool + base);
+            for (int i = lane; i < TILE_LINES; i += 32) {
+              asm volatile("prefetch.global.L2 [%0];" ::"l"(kb + (size_t)i * 128));
+              asm volatile("prefetch.global.L2 [%0];" ::"l"(vb + (size_t)i * 128));
+            }
+          }
+        }
         grid_barrier();
       }
 
       // ---------------- P2: attention (as in decode_mega.cu): block b < kv_heads * nsp takes (kv head, split)
-      const int nsp = min(RING_MAX_SPLIT, max(1, (ntiles + a.attn_tiles_per_block - 1) / a.attn_tiles_per_block));
       {
         float* qs = att;                                           // [G][D]
         float* part = att + G * D;                                 // [RW][G][PS]
