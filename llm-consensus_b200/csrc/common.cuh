@@ -64,6 +64,27 @@ __device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepc
 __device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
 #endif
 
+#ifdef __CUDACC__
+// Launch with (pdl = true) or without the programmatic-dependent-launch attribute.  A kernel launched with it MUST
+// execute pdl_wait() before it reads anything its predecessor wrote (and before it writes anything the predecessor
+// reads); everything before that point overlaps the predecessor's tail.
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_maybe_pdl(void (*kern)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t s, bool pdl,
+                                    Args... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = s;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = pdl ? 1 : 0;
+  return cudaLaunchKernelEx(&cfg, kern, static_cast<KArgs>(args)...);
+}
+#endif
+
 // ---------------------------------------------------------------- host error plumbing
 struct Status {
   int code = LLMC_OK;

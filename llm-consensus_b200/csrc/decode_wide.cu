@@ -40,6 +40,8 @@ __global__ void rope_append_batch_kernel(const float* __restrict__ qkv, const in
                                          int page_size, int q_heads, int kv_heads, int d, float* __restrict__ q_out) {
   const int b = blockIdx.x, h = blockIdx.y, i = threadIdx.x;
   const int hd2 = d >> 1;
+  pdl_launch_dependents();
+  pdl_wait();
   if (i >= hd2) return;
   const int slot = slots[b];
   const int pos = seq_len[slot];
@@ -76,6 +78,8 @@ __global__ void rope_append_batch_kernel(const float* __restrict__ qkv, const in
 
 __global__ void __launch_bounds__(256) split_rows_kernel(const float* __restrict__ x, size_t n4,
                                                          uint16_t* __restrict__ hi, uint16_t* __restrict__ lo) {
+  pdl_launch_dependents();
+  pdl_wait();
   for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += (size_t)gridDim.x * blockDim.x) {
     const float4 v = *reinterpret_cast<const float4*>(x + 4 * i);
     const float y[4] = {v.x, v.y, v.z, v.w};
@@ -167,20 +171,18 @@ cudaError_t launch_embed_slots(const uint16_t* emb, const int* next_token, const
 cudaError_t launch_rope_append_batch(const float* qkv, int B, const int* slots, const int* seq_len,
                                      const float* rope_cos, const float* rope_sin, const int* block_table,
                                      int bt_stride, void* kpool, void* vpool, int kv_fp32, int page_size, int q_heads,
-                                     int kv_heads, int head_dim, float* q_out, cudaStream_t s) {
+                                     int kv_heads, int head_dim, float* q_out, cudaStream_t s, bool pdl) {
   dim3 grid(B, q_heads + 2 * kv_heads);
-  rope_append_batch_kernel<<<grid, head_dim / 2 < 32 ? 32 : head_dim / 2, 0, s>>>(
-      qkv, slots, seq_len, rope_cos, rope_sin, block_table, bt_stride, kpool, vpool, kv_fp32, page_size, q_heads,
-      kv_heads, head_dim, q_out);
-  return cudaGetLastError();
+  return launch_maybe_pdl(rope_append_batch_kernel, grid, dim3(head_dim / 2 < 32 ? 32 : head_dim / 2), 0, s, pdl, qkv,
+                          slots, seq_len, rope_cos, rope_sin, block_table, bt_stride, kpool, vpool, kv_fp32, page_size,
+                          q_heads, kv_heads, head_dim, q_out);
 }
 
-cudaError_t launch_split_rows(const float* x, size_t n, uint16_t* hi, uint16_t* lo, cudaStream_t s) {
+cudaError_t launch_split_rows(const float* x, size_t n, uint16_t* hi, uint16_t* lo, cudaStream_t s, bool pdl) {
   if (n % 4) return cudaErrorInvalidValue;
   const size_t n4 = n / 4;
   const int blocks = (int)std::min<size_t>((n4 + 255) / 256, 1184);
-  split_rows_kernel<<<blocks, 256, 0, s>>>(x, n4, hi, lo);
-  return cudaGetLastError();
+  return launch_maybe_pdl(split_rows_kernel, dim3(blocks), dim3(256), 0, s, pdl, x, n4, hi, lo);
 }
 
 size_t argmax_scratch_elems(int B) { return (size_t)B * AM_CHUNKS; }

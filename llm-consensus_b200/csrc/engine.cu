@@ -167,8 +167,9 @@ int gemm(llmc_engine* e, const uint16_t* A, const uint16_t* Alo, const uint16_t*
          int N, int K, int epi, bool decode = false) {
   // up to 32 rows the swapped-operand decode kernel wins (deeper weight pipeline); above, the prefill kernel + split-K
   if (e->prefill_impl == 0 && decode && T <= 32 && gemm_decode_tc_supported(T, N, K, epi))
-    E_TRY(launch_gemm_decode_tc(A, Alo, W, out, out_lo, T, N, K, epi, e->stream));
-  else if (e->prefill_impl == 0) E_TRY(launch_gemm_tcgen05(A, Alo, W, out, out_lo, T, N, K, epi, e->stream, decode));
+    E_TRY(launch_gemm_decode_tc(A, Alo, W, out, out_lo, T, N, K, epi, e->stream, e->use_pdl));
+  else if (e->prefill_impl == 0)
+    E_TRY(launch_gemm_tcgen05(A, Alo, W, out, out_lo, T, N, K, epi, e->stream, decode, decode && e->use_pdl));
   else E_TRY(launch_gemm_simple(A, Alo, W, out, out_lo, T, N, K, epi, e->stream));
   e->stats.kernel_launches++;
   return LLMC_OK;
@@ -221,16 +222,19 @@ int enqueue_wide_step(llmc_engine* e, int B, int nsplit) {
   const ModelDims& d = e->d;
   const int H = d.hidden, QD = d.qd(), KD = d.kd(), I = d.inter, V = d.vocab;
   cudaStream_t s = e->stream;
+  const bool pdl = e->use_pdl;
   E_TRY(launch_embed_slots(e->emb, e->d_next_token, e->d_slots, B, H, e->px, s));
   for (int l = 0; l < d.layers; ++l) {
     const LayerW& w = e->L[l];
     unsigned char* kp = e->kpool + (size_t)l * e->kv_layer_stride * e->kv_elem;
     unsigned char* vp = e->vpool + (size_t)l * e->kv_layer_stride * e->kv_elem;
-    E_TRY(launch_rmsnorm_rows(e->px, w.g1, d.rms_eps, B, H, e->pxn, e->pxn_lo, s));
-    if (int rc = gemm(e, e->pxn, e->pxn_lo, w.wqkv, e->pqkv, nullptr, B, QD + 2 * KD, H, GEMM_STORE_F32, true)) return rc;
+    // the norm kernel also clears the QKV buffer, so the split-K GEMM can accumulate into it (no memset node, which
+    // would cut the chain of programmatic dependent launches)
+    E_TRY(launch_rmsnorm_rows(e->px, w.g1, d.rms_eps, B, H, e->pxn, e->pxn_lo, s, pdl, e->pqkv, QD + 2 * KD));
+    if (int rc = gemm(e, e->pxn, e->pxn_lo, w.wqkv, e->pqkv, nullptr, B, QD + 2 * KD, H, GEMM_RESID_F32, true)) return rc;
     E_TRY(launch_rope_append_batch(e->pqkv, B, e->d_slots, e->d_seq_len, e->rope_cos, e->rope_sin, e->d_block_table,
                                    e->pages_per_seq, kp, vp, e->kv_fp32, e->page_size, d.q_heads, d.kv_heads,
-                                   d.head_dim, e->q, s));
+                                   d.head_dim, e->q, s, pdl));
     {
       AttnDecodeArgs a;
       memset(&a, 0, sizeof(a));
@@ -239,15 +243,15 @@ int enqueue_wide_step(llmc_engine* e, int B, int nsplit) {
       a.block_table = e->d_block_table; a.bt_stride = e->pages_per_seq;
       a.page_size = e->page_size; a.q_heads = d.q_heads; a.kv_heads = d.kv_heads; a.head_dim = d.head_dim;
       a.B = B; a.nsplit = nsplit; a.scratch = e->attn_scratch; a.counters = e->attn_counters;
-      E_TRY(launch_attn_decode(a, false, s));
+      E_TRY(launch_attn_decode(a, pdl, s));
     }
-    E_TRY(launch_split_rows(e->attn, (size_t)B * QD, e->pattn, e->pattn_lo, s));
+    E_TRY(launch_split_rows(e->attn, (size_t)B * QD, e->pattn, e->pattn_lo, s, pdl));
     if (int rc = gemm(e, e->pattn, e->pattn_lo, w.wo, e->px, nullptr, B, H, QD, GEMM_RESID_F32, true)) return rc;
-    E_TRY(launch_rmsnorm_rows(e->px, w.g2, d.rms_eps, B, H, e->pxn, e->pxn_lo, s));
+    E_TRY(launch_rmsnorm_rows(e->px, w.g2, d.rms_eps, B, H, e->pxn, e->pxn_lo, s, pdl));
     if (int rc = gemm(e, e->pxn, e->pxn_lo, w.wgu, e->pact, e->pact_lo, B, 2 * I, H, GEMM_SWIGLU_BF16, true)) return rc;
     if (int rc = gemm(e, e->pact, e->pact_lo, w.wd, e->px, nullptr, B, H, I, GEMM_RESID_F32, true)) return rc;
   }
-  E_TRY(launch_rmsnorm_rows(e->px, e->gf, d.rms_eps, B, H, e->pxn, e->pxn_lo, s));
+  E_TRY(launch_rmsnorm_rows(e->px, e->gf, d.rms_eps, B, H, e->pxn, e->pxn_lo, s, pdl));
   if (int rc = gemm(e, e->pxn, e->pxn_lo, e->lmhead, e->logits, nullptr, B, V, H, GEMM_STORE_F32, true)) return rc;
   E_TRY(launch_argmax_finalise(e->logits, B, V, e->d_slots, e->d_next_token, e->d_seq_len, e->d_out_tokens,
                                MAX_STEPS_PER_CALL, e->d_step_counter, e->lm_counter, e->part_val, e->part_idx, s));

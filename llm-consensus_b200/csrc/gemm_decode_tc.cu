@@ -93,10 +93,24 @@ __global__ void __launch_bounds__(DTHREADS, 1)
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *reinterpret_cast<volatile uint32_t*>(tmem_slot);
+  pdl_launch_dependents();   // the next kernel of the step may start its own prologue
 
   if (warp == 0) {
     if (lane == 0) {
-      for (int kb = 0; kb < KB; ++kb) {
+      // Weights never depend on the previous kernel: the first ring of weight tiles is requested BEFORE the
+      // programmatic-dependency wait, the activation tiles (written by the previous kernel) after it.
+      const int pre = KB < C::STAGES ? KB : C::STAGES;
+      for (int kb = 0; kb < pre; ++kb) {
+        mbar_expect_tx(full_bar(kb), C::TX_BYTES);
+        tma_load_2d(base + kb * C::STAGE_BYTES, &tmW, (kb0 + kb) * DK, n0, full_bar(kb));
+      }
+      pdl_wait();
+      for (int kb = 0; kb < pre; ++kb) {
+        const uint32_t sw = base + kb * C::STAGE_BYTES;
+        tma_load_2d(sw + C::W_BYTES, &tmA, (kb0 + kb) * DK, 0, full_bar(kb));
+        if (SPLIT) tma_load_2d(sw + C::W_BYTES + C::A_ALLOC, &tmAlo, (kb0 + kb) * DK, 0, full_bar(kb));
+      }
+      for (int kb = pre; kb < KB; ++kb) {
         const int s = kb % C::STAGES;
         const uint32_t ph = (kb / C::STAGES) & 1;
         mbar_wait(empty_bar(s), ph ^ 1u);
@@ -134,6 +148,7 @@ __global__ void __launch_bounds__(DTHREADS, 1)
     // ---- epilogue: warp w may only touch TMEM lanes [32*(w%4), +32) = weight rows n0 + 32*(w%4) + lane
     const int quad = warp & 3;
     const int r = quad * 32 + lane;        // row inside the tile
+    pdl_wait();                            // outputs (and the residual read) must follow the previous kernel
     mbar_wait(tmem_full_bar, 0);
     tc_fence_after();
     const uint32_t tq = tmem_base + ((uint32_t)(quad * 32) << 16);
@@ -209,7 +224,7 @@ int pick_ksplit(int tiles, int kblocks) {
 
 template <int NB, int EPI, bool SPLIT>
 cudaError_t launch_nb(const uint16_t* A, const uint16_t* Alo, const uint16_t* W, void* out, void* out_lo, int B, int N,
-                      int K, cudaStream_t s) {
+                      int K, cudaStream_t s, bool pdl) {
   using C = DCfg<NB, SPLIT>;
   CUtensorMap ma, ml, mw;
   if (!make_map(&ma, A, (uint64_t)B, (uint64_t)K, NB) || !make_map(&mw, W, (uint64_t)N, (uint64_t)K, DM) ||
@@ -224,26 +239,27 @@ cudaError_t launch_nb(const uint16_t* A, const uint16_t* Alo, const uint16_t* W,
     e = cudaMemsetAsync(out, 0, (size_t)B * N * sizeof(float), s);
     if (e != cudaSuccess) return e;
   }
-  kern<<<dim3(tiles, 1, ks), DTHREADS, C::SMEM, s>>>(ma, ml, mw, out, out_lo, B, N, K);
-  return cudaGetLastError();
+  // (a memset node in front of the kernel is an ordinary dependency: no programmatic edge then)
+  return launch_maybe_pdl(kern, dim3(tiles, 1, ks), dim3(DTHREADS), (size_t)C::SMEM, s,
+                          pdl && !(ks > 1 && EPI == GEMM_STORE_F32), ma, ml, mw, out, out_lo, B, N, K);
 }
 
 template <int EPI, bool SPLIT>
 cudaError_t launch_b(const uint16_t* A, const uint16_t* Alo, const uint16_t* W, void* out, void* out_lo, int B, int N,
-                     int K, cudaStream_t s) {
-  if (B <= 16) return launch_nb<16, EPI, SPLIT>(A, Alo, W, out, out_lo, B, N, K, s);
-  if (B <= 32) return launch_nb<32, EPI, SPLIT>(A, Alo, W, out, out_lo, B, N, K, s);
-  if (B <= 64) return launch_nb<64, EPI, SPLIT>(A, Alo, W, out, out_lo, B, N, K, s);
-  return launch_nb<128, EPI, SPLIT>(A, Alo, W, out, out_lo, B, N, K, s);
+                     int K, cudaStream_t s, bool pdl) {
+  if (B <= 16) return launch_nb<16, EPI, SPLIT>(A, Alo, W, out, out_lo, B, N, K, s, pdl);
+  if (B <= 32) return launch_nb<32, EPI, SPLIT>(A, Alo, W, out, out_lo, B, N, K, s, pdl);
+  if (B <= 64) return launch_nb<64, EPI, SPLIT>(A, Alo, W, out, out_lo, B, N, K, s, pdl);
+  return launch_nb<128, EPI, SPLIT>(A, Alo, W, out, out_lo, B, N, K, s, pdl);
 }
 
 template <bool SPLIT>
 cudaError_t launch_e(const uint16_t* A, const uint16_t* Alo, const uint16_t* W, void* out, void* out_lo, int B, int N,
-                     int K, int epi, cudaStream_t s) {
+                     int K, int epi, cudaStream_t s, bool pdl) {
   switch (epi) {
-    case GEMM_STORE_F32: return launch_b<GEMM_STORE_F32, SPLIT>(A, Alo, W, out, out_lo, B, N, K, s);
-    case GEMM_RESID_F32: return launch_b<GEMM_RESID_F32, SPLIT>(A, Alo, W, out, out_lo, B, N, K, s);
-    case GEMM_SWIGLU_BF16: return launch_b<GEMM_SWIGLU_BF16, SPLIT>(A, Alo, W, out, out_lo, B, N, K, s);
+    case GEMM_STORE_F32: return launch_b<GEMM_STORE_F32, SPLIT>(A, Alo, W, out, out_lo, B, N, K, s, pdl);
+    case GEMM_RESID_F32: return launch_b<GEMM_RESID_F32, SPLIT>(A, Alo, W, out, out_lo, B, N, K, s, pdl);
+    case GEMM_SWIGLU_BF16: return launch_b<GEMM_SWIGLU_BF16, SPLIT>(A, Alo, W, out, out_lo, B, N, K, s, pdl);
   }
   return cudaErrorInvalidValue;
 }
@@ -256,10 +272,10 @@ bool gemm_decode_tc_supported(int B, int N, int K, int epi) {
 }
 
 cudaError_t launch_gemm_decode_tc(const uint16_t* A, const uint16_t* Alo, const uint16_t* W, void* out, void* out_lo,
-                                  int B, int N, int K, int epi, cudaStream_t s) {
+                                  int B, int N, int K, int epi, cudaStream_t s, bool pdl) {
   if (!gemm_decode_tc_supported(B, N, K, epi)) return cudaErrorInvalidValue;
-  return Alo ? launch_e<true>(A, Alo, W, out, out_lo, B, N, K, epi, s)
-             : launch_e<false>(A, Alo, W, out, out_lo, B, N, K, epi, s);
+  return Alo ? launch_e<true>(A, Alo, W, out, out_lo, B, N, K, epi, s, pdl)
+             : launch_e<false>(A, Alo, W, out, out_lo, B, N, K, epi, s, pdl);
 }
 
 }  // namespace llmc

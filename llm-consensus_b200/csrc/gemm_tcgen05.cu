@@ -84,9 +84,23 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1)
   tc_fence_after();
   const uint32_t tmem_base = *reinterpret_cast<volatile uint32_t*>(tmem_slot);
 
+  pdl_launch_dependents();   // no-ops unless launched with the programmatic-dependent-launch attribute (wide decode)
   if (warp == 0) {
     if (lane == 0) {
-      for (int kb = 0; kb < KB; ++kb) {
+      // weights never depend on the previous kernel: the first ring of W tiles is requested before the
+      // programmatic-dependency wait, the activation tiles after it
+      const int pre = KB < C::STAGES ? KB : C::STAGES;
+      for (int kb = 0; kb < pre; ++kb) {
+        mbar_expect_tx(full_bar(kb), C::STAGE_BYTES);
+        tma_load_2d(base + kb * C::STAGE_BYTES + C::A_TILES * C::A_BYTES, &tmW, (kb0 + kb) * BK, n0, full_bar(kb));
+      }
+      pdl_wait();
+      for (int kb = 0; kb < pre; ++kb) {
+        const uint32_t sa = base + kb * C::STAGE_BYTES;
+        tma_load_2d(sa, &tmA, (kb0 + kb) * BK, m0, full_bar(kb));
+        if (SPLIT) tma_load_2d(sa + C::A_BYTES, &tmAlo, (kb0 + kb) * BK, m0, full_bar(kb));
+      }
+      for (int kb = pre; kb < KB; ++kb) {
         const int s = kb % C::STAGES;
         const uint32_t ph = (kb / C::STAGES) & 1;
         mbar_wait(empty_bar(s), ph ^ 1u);
@@ -124,6 +138,7 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1)
     // ---- epilogue: warp w may only touch TMEM lanes [32*(w%4), +32)
     const int quad = warp & 3;
     const int row = m0 + quad * 32 + lane;
+    pdl_wait();
     mbar_wait(tmem_full_bar, 0);
     tc_fence_after();
     const uint32_t tq = tmem_base + ((uint32_t)(quad * 32) << 16);
@@ -212,7 +227,7 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1)
 
 template <int BN, int EPI, bool SPLIT>
 cudaError_t launch_tile(const uint16_t* A, const uint16_t* Alo, const uint16_t* W, void* out, void* out_lo, int T,
-                        int N, int K, cudaStream_t s, int ksplit = 1) {
+                        int N, int K, cudaStream_t s, int ksplit = 1, bool pdl = false) {
   CUtensorMap ma, ml, mw;
   if (!make_map(&ma, A, (uint64_t)T, (uint64_t)K, BM) || !make_map(&mw, W, (uint64_t)N, (uint64_t)K, BN) ||
       !make_map(&ml, SPLIT ? Alo : A, (uint64_t)T, (uint64_t)K, BM))
@@ -225,8 +240,9 @@ cudaError_t launch_tile(const uint16_t* A, const uint16_t* Alo, const uint16_t* 
     e = cudaMemsetAsync(out, 0, (size_t)T * N * sizeof(float), s);
     if (e != cudaSuccess) return e;
   }
-  kern<<<grid, GEMM_THREADS, TileCfg<BN, SPLIT>::SMEM, s>>>(ma, ml, mw, out, out_lo, T, N, K);
-  return cudaGetLastError();
+  // decode-shaped calls (ksplit allowed) are part of a programmatic-dependent-launch chain unless a memset precedes
+  return launch_maybe_pdl(kern, grid, dim3(GEMM_THREADS), (size_t)TileCfg<BN, SPLIT>::SMEM, s,
+                          pdl && !(ksplit > 1 && EPI == GEMM_STORE_F32), ma, ml, mw, out, out_lo, T, N, K);
 }
 
 // largest power-of-two split of the k-blocks that keeps the grid within about one wave and >= 4 k-blocks per CTA
@@ -238,7 +254,7 @@ int pick_ksplit(int tiles, int kblocks) {
 
 template <int EPI, bool SPLIT>
 cudaError_t launch_epi(const uint16_t* A, const uint16_t* Alo, const uint16_t* W, void* out, void* out_lo, int T,
-                       int N, int K, cudaStream_t s, bool allow_ksplit) {
+                       int N, int K, cudaStream_t s, bool allow_ksplit, bool pdl) {
   // pick the widest tile that still yields at least ~one wave of CTAs on 148 SMs
   const int mt = (T + BM - 1) / BM;
   if constexpr (EPI == GEMM_STORE_F32 || EPI == GEMM_RESID_F32) {
@@ -246,27 +262,27 @@ cudaError_t launch_epi(const uint16_t* A, const uint16_t* Alo, const uint16_t* W
     // are re-read from L2 by few CTAs and every SM still has work
     if (allow_ksplit && mt == 1 && N % 128 == 0 && N / 128 < 148) {
       const int ks = pick_ksplit(N / 128, K / BK);
-      if (ks > 1) return launch_tile<128, EPI, SPLIT>(A, Alo, W, out, out_lo, T, N, K, s, ks);
+      if (ks > 1) return launch_tile<128, EPI, SPLIT>(A, Alo, W, out, out_lo, T, N, K, s, ks, pdl);
     }
   }
-  if (N % 256 == 0 && (N / 256) * mt >= 148) return launch_tile<256, EPI, SPLIT>(A, Alo, W, out, out_lo, T, N, K, s);
+  if (N % 256 == 0 && (N / 256) * mt >= 148) return launch_tile<256, EPI, SPLIT>(A, Alo, W, out, out_lo, T, N, K, s, 1, pdl);
   if constexpr (EPI == GEMM_SWIGLU_BF16) {
     if (N % 128 != 0) return cudaErrorInvalidValue;
-    return launch_tile<128, EPI, SPLIT>(A, Alo, W, out, out_lo, T, N, K, s);
+    return launch_tile<128, EPI, SPLIT>(A, Alo, W, out, out_lo, T, N, K, s, 1, pdl);
   } else {
-    if (N % 128 == 0 && (N / 128) * mt >= 148) return launch_tile<128, EPI, SPLIT>(A, Alo, W, out, out_lo, T, N, K, s);
-    return launch_tile<64, EPI, SPLIT>(A, Alo, W, out, out_lo, T, N, K, s);
+    if (N % 128 == 0 && (N / 128) * mt >= 148) return launch_tile<128, EPI, SPLIT>(A, Alo, W, out, out_lo, T, N, K, s, 1, pdl);
+    return launch_tile<64, EPI, SPLIT>(A, Alo, W, out, out_lo, T, N, K, s, 1, pdl);
   }
 }
 
 template <bool SPLIT>
 cudaError_t launch_split(const uint16_t* A, const uint16_t* Alo, const uint16_t* W, void* out, void* out_lo, int T,
-                         int N, int K, int epi, cudaStream_t s, bool ks) {
+                         int N, int K, int epi, cudaStream_t s, bool ks, bool pdl) {
   switch (epi) {
-    case GEMM_STORE_BF16: return launch_epi<GEMM_STORE_BF16, SPLIT>(A, Alo, W, out, out_lo, T, N, K, s, ks);
-    case GEMM_STORE_F32: return launch_epi<GEMM_STORE_F32, SPLIT>(A, Alo, W, out, out_lo, T, N, K, s, ks);
-    case GEMM_RESID_F32: return launch_epi<GEMM_RESID_F32, SPLIT>(A, Alo, W, out, out_lo, T, N, K, s, ks);
-    case GEMM_SWIGLU_BF16: return launch_epi<GEMM_SWIGLU_BF16, SPLIT>(A, Alo, W, out, out_lo, T, N, K, s, ks);
+    case GEMM_STORE_BF16: return launch_epi<GEMM_STORE_BF16, SPLIT>(A, Alo, W, out, out_lo, T, N, K, s, ks, pdl);
+    case GEMM_STORE_F32: return launch_epi<GEMM_STORE_F32, SPLIT>(A, Alo, W, out, out_lo, T, N, K, s, ks, pdl);
+    case GEMM_RESID_F32: return launch_epi<GEMM_RESID_F32, SPLIT>(A, Alo, W, out, out_lo, T, N, K, s, ks, pdl);
+    case GEMM_SWIGLU_BF16: return launch_epi<GEMM_SWIGLU_BF16, SPLIT>(A, Alo, W, out, out_lo, T, N, K, s, ks, pdl);
   }
   return cudaErrorInvalidValue;
 }
@@ -274,10 +290,10 @@ cudaError_t launch_split(const uint16_t* A, const uint16_t* Alo, const uint16_t*
 }  // namespace
 
 cudaError_t launch_gemm_tcgen05(const uint16_t* A, const uint16_t* Alo, const uint16_t* W, void* out, void* out_lo,
-                                int T, int N, int K, int epi, cudaStream_t s, bool allow_ksplit) {
+                                int T, int N, int K, int epi, cudaStream_t s, bool allow_ksplit, bool pdl) {
   if (K % BK != 0 || T < 1 || N % 64 != 0) return cudaErrorInvalidValue;
-  return Alo ? launch_split<true>(A, Alo, W, out, out_lo, T, N, K, epi, s, allow_ksplit)
-             : launch_split<false>(A, Alo, W, out, out_lo, T, N, K, epi, s, allow_ksplit);
+  return Alo ? launch_split<true>(A, Alo, W, out, out_lo, T, N, K, epi, s, allow_ksplit, pdl)
+             : launch_split<false>(A, Alo, W, out, out_lo, T, N, K, epi, s, allow_ksplit, pdl);
 }
 
 }  // namespace llmc

@@ -132,7 +132,8 @@ cudaError_t launch_embed_rows(const uint16_t* emb, const int* tokens, int T, int
 // RMSNorm of fp32 rows -> bf16 GEMM operand.  out_lo != NULL: split form, x = hi + lo with both bf16
 // (the pair carries 16 mantissa bits; the GEMM then accumulates A_hi W + A_lo W).
 cudaError_t launch_rmsnorm_rows(const float* x, const uint16_t* gain, float eps, int T, int H, uint16_t* out_hi,
-                                uint16_t* out_lo, cudaStream_t s);
+                                uint16_t* out_lo, cudaStream_t s, bool pdl = false, float* zero_rows = nullptr,
+                                int zero_cols = 0);
 // qkv fp32 [T][qd+2kd] -> q fp32 [T][qd] (RoPE), k/v appended to the pages at positions p0..p0+T-1
 cudaError_t launch_rope_append(const float* qkv, int T, int p0, int slot, const float* rope_cos,
                                const float* rope_sin, const int* block_table, int bt_stride, void* kpool,
@@ -160,8 +161,8 @@ cudaError_t launch_embed_slots(const uint16_t* emb, const int* next_token, const
 cudaError_t launch_rope_append_batch(const float* qkv, int B, const int* slots, const int* seq_len,
                                      const float* rope_cos, const float* rope_sin, const int* block_table,
                                      int bt_stride, void* kpool, void* vpool, int kv_fp32, int page_size, int q_heads,
-                                     int kv_heads, int head_dim, float* q_out, cudaStream_t s);
-cudaError_t launch_split_rows(const float* x, size_t n, uint16_t* hi, uint16_t* lo, cudaStream_t s);
+                                     int kv_heads, int head_dim, float* q_out, cudaStream_t s, bool pdl = false);
+cudaError_t launch_split_rows(const float* x, size_t n, uint16_t* hi, uint16_t* lo, cudaStream_t s, bool pdl = false);
 // greedy argmax of B logit rows (lowest index on ties); writes next_token / seq_len (+1) / out_tokens[b][*step_counter]
 // and advances the step counter once per launch
 size_t argmax_scratch_elems(int B);   // part_val / part_idx sizes
@@ -180,13 +181,14 @@ enum GemmEpi {
 // allow_ksplit: decode-shaped calls (T <= 128, fp32 output) may split K over several CTAs per output tile, which add
 // their partial sums with fp32 reductions (summation order then varies from run to run in the last bits)
 cudaError_t launch_gemm_tcgen05(const uint16_t* A_hi, const uint16_t* A_lo, const uint16_t* W, void* out,
-                                void* out_lo, int T, int N, int K, int epi, cudaStream_t s, bool allow_ksplit = false);
+                                void* out_lo, int T, int N, int K, int epi, cudaStream_t s, bool allow_ksplit = false,
+                                bool pdl = false);
 // ------------------------------------------------------------------ gemm_decode_tc.cu (decode, <= 128 sequences)
 // Same product with the operands swapped on the tensor cores (weights = M tile, batch = N): out[B][N] fp32 store /
 // residual add / SwiGLU (bf16 hi [, lo]); split-K where a matrix has few row tiles.
 bool gemm_decode_tc_supported(int B, int N, int K, int epi);
 cudaError_t launch_gemm_decode_tc(const uint16_t* A_hi, const uint16_t* A_lo, const uint16_t* W, void* out,
-                                  void* out_lo, int B, int N, int K, int epi, cudaStream_t s);
+                                  void* out_lo, int B, int N, int K, int epi, cudaStream_t s, bool pdl = false);
 cudaError_t launch_gemm_simple(const uint16_t* A_hi, const uint16_t* A_lo, const uint16_t* W, void* out,
                                void* out_lo, int T, int N, int K, int epi, cudaStream_t s);
 

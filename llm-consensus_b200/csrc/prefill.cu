@@ -37,12 +37,20 @@ __device__ __forceinline__ void split_bf16(float v, uint16_t& hi, uint16_t& lo) 
 
 // one block (256 threads) per row; two passes over a row that stays in L1/L2
 
+// zero_row != NULL: the block also clears row t (zero_cols floats) of another buffer -- the wide decode step uses
+// it to prepare the accumulation target of the following split-K GEMM without a separate memset node
 __global__ void __launch_bounds__(256) rmsnorm_rows_kernel(const float* __restrict__ x, const uint16_t* __restrict__ gain,
                                                            float eps, int T, int H, uint16_t* __restrict__ out,
-                                                           uint16_t* __restrict__ out_lo) {
+                                                           uint16_t* __restrict__ out_lo, float* __restrict__ zero_row,
+                                                           int zero_cols) {
   __shared__ float red[8];
   const int t = blockIdx.x, tid = threadIdx.x;
   const float* xr = x + (size_t)t * H;
+  pdl_launch_dependents();
+  pdl_wait();
+  if (zero_row)
+    for (int k = tid * 4; k < zero_cols; k += 256 * 4)
+      *reinterpret_cast<float4*>(zero_row + (size_t)t * zero_cols + k) = make_float4(0.f, 0.f, 0.f, 0.f);
   float ss = 0.f;
   for (int k = tid * 4; k < H; k += 256 * 4) {
     float4 v = *reinterpret_cast<const float4*>(xr + k);
@@ -237,9 +245,10 @@ cudaError_t launch_embed_rows(const uint16_t* emb, const int* tokens, int T, int
 }
 
 cudaError_t launch_rmsnorm_rows(const float* x, const uint16_t* gain, float eps, int T, int H, uint16_t* out_hi,
-                                uint16_t* out_lo, cudaStream_t s) {
-  rmsnorm_rows_kernel<<<T, 256, 0, s>>>(x, gain, eps, T, H, out_hi, out_lo);
-  return cudaGetLastError();
+                                uint16_t* out_lo, cudaStream_t s, bool pdl, float* zero_rows, int zero_cols) {
+  if (zero_rows && zero_cols % 4) return cudaErrorInvalidValue;
+  return launch_maybe_pdl(rmsnorm_rows_kernel, dim3(T), dim3(256), 0, s, pdl, x, gain, eps, T, H, out_hi, out_lo,
+                          zero_rows, zero_cols);
 }
 
 cudaError_t launch_rope_append(const float* qkv, int T, int p0, int slot, const float* rope_cos,
