@@ -393,7 +393,7 @@ static int create_impl(llmc_engine* e, const llmc_config& c) {
   e->use_mega = !(c.flags & LLMC_FLAG_NO_MEGAKERNEL);
   {
     const char* wm = getenv("LLMC_WIDE_MIN_BATCH");   // experiment knob: smallest batch served by the wide (GEMM) decode path
-    e->wide_min_batch = wm ? std::max(2, atoi(wm)) : 4;
+    e->wide_min_batch = wm ? std::max(2, atoi(wm)) : 2;
     if (e->wide_min_batch > MAX_GEMV_BATCH + 1) e->wide_min_batch = MAX_GEMV_BATCH + 1;
   }
   e->use_ring = e->use_mega && !(c.flags & LLMC_FLAG_NO_RING) &&

@@ -66,7 +66,7 @@ struct llmc_engine {
   uint16_t* pattn_ws = nullptr;  // split K/V workspace of the tensor-core prefill attention (one layer, max_ctx positions)
   // one-kernel batch-1 decode
   bool use_mega = true;
-  int wide_min_batch = 4;  // batches >= this use the wide (GEMM) decode path; smaller ones the GEMV kernels
+  int wide_min_batch = 2;  // batches >= this use the wide (GEMM) decode path (LLMC_WIDE_MIN_BATCH=9: GEMV kernels up to 8)
   bool use_ring = false;  // persistent batch-1 decode through the TMA shared-memory ring (decode_ring.cu)
   llmc::MegaLayer* d_mega_layers = nullptr;
   float* mega_scratch = nullptr;
