@@ -50,9 +50,11 @@ struct KvTraits<float> {
   }
 };
 
-template <int D, int G, typename KVT>
-__global__ void __launch_bounds__(AttnCfg<D, G>::AWARPS * 32) attn_decode_kernel(const AttnDecodeArgs a) {
-  constexpr int AWARPS = AttnCfg<D, G>::AWARPS;
+// AWARPS: warps per block.  Few (sequence, kv head) pairs: 16 (8) warps share one pair so that a long context is
+// covered by many tiles in flight.  Many pairs (wide batches): 4 warps per block, so that several blocks are resident
+// per SM and the staging / merge phases of one overlap the tile loads of the others.
+template <int D, int G, typename KVT, int AWARPS>
+__global__ void __launch_bounds__(AWARPS * 32, AWARPS == 4 ? 4 : 1) attn_decode_kernel(const AttnDecodeArgs a) {
   using M = LaneMap<D, G, KVT>;
   constexpr int EPV = M::EPV, LPR = M::LPR, CPL = M::CPL, RPP = M::RPP, NP = M::NP, EPL = M::EPL, PPG = M::PPG;
   constexpr int DPL = D / 32;                       // dims per lane in the final merge
@@ -168,11 +170,10 @@ __global__ void __launch_bounds__(AttnCfg<D, G>::AWARPS * 32) attn_decode_kernel
   if (tid == 0) *ctr = 0u;
 }
 
-template <int D, int G, typename KVT>
-cudaError_t launch_t(const AttnDecodeArgs& a, bool pdl, cudaStream_t s) {
-  constexpr int AWARPS = AttnCfg<D, G>::AWARPS;
+template <int D, int G, typename KVT, int AWARPS>
+cudaError_t launch_w(const AttnDecodeArgs& a, bool pdl, cudaStream_t s) {
   const size_t smem = ((size_t)G * D + (size_t)AWARPS * G * (D + 2) + (size_t)AWARPS * G * (TP + 1)) * sizeof(float);
-  auto kern = attn_decode_kernel<D, G, KVT>;
+  auto kern = attn_decode_kernel<D, G, KVT, AWARPS>;
   if (smem > 48 * 1024) {
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
@@ -188,6 +189,13 @@ cudaError_t launch_t(const AttnDecodeArgs& a, bool pdl, cudaStream_t s) {
   cfg.attrs = attr;
   cfg.numAttrs = pdl ? 1 : 0;
   return cudaLaunchKernelEx(&cfg, kern, a);
+}
+
+template <int D, int G, typename KVT>
+cudaError_t launch_t(const AttnDecodeArgs& a, bool pdl, cudaStream_t s) {
+  // two waves of blocks or more: small blocks, several resident per SM (measured: worse below that)
+  if ((long long)a.nsplit * a.kv_heads * a.B >= 2 * 148) return launch_w<D, G, KVT, 4>(a, pdl, s);
+  return launch_w<D, G, KVT, AttnCfg<D, G>::AWARPS>(a, pdl, s);
 }
 
 template <int D, typename KVT>
