@@ -348,3 +348,31 @@ def test_config2_llama1b_512_prompt_256_decode(gpu):
     st = e.stats()
     assert st["kernel_launches"] > 0
     e.close()
+
+
+def test_wide_batch_decode_full_size_1b(gpu):
+    """The wide decode path (tcgen05 skinny GEMMs, split-K, batched RoPE/append, two-stage argmax) at the full
+    Llama-3.2-1B shape: 12 sequences of different lengths decoded together, each against its own oracle run."""
+    B, n_new = 12, 6
+    o = ref.Oracle("llama-1b", seed=0, max_ctx=128)
+    e = gpu.Engine(shape=gpu.SHAPE_LLAMA_1B, seed=0, max_ctx=128, max_slots=B, prefill_impl=DEFAULT_IMPL)
+    rng = np.random.default_rng(77)
+    prompts = [rng.integers(0, 128256, int(n)) for n in rng.integers(5, 60, B)]
+    slots, firsts = [], []
+    for p in prompts:
+        s = e.seq_alloc()
+        slots.append(s)
+        firsts.append(e.prefill(s, p))
+    out, lg = e.decode(slots, n_new, want_logits=True)
+    worst = 0.0
+    for i, p in enumerate(prompts):
+        o.reset()
+        otoks, olog = o.generate(p, n_new + 1, want_logits=True)
+        gt = [firsts[i]] + out[i].tolist()
+        where, margin = greedy_agreement(otoks, olog, gt)
+        assert where < 0, (i, where, margin)
+        if where == -1:
+            worst = max(worst, float(np.abs(lg[i] - olog[n_new]).max()))
+    print("wide decode, 1B shape, %d sequences: worst last-step logit err %.3e" % (B, worst))
+    assert worst <= TOL
+    e.close()
