@@ -53,6 +53,17 @@ struct KvTraits<float> {
 // AWARPS: warps per block.  Few (sequence, kv head) pairs: 16 (8) warps share one pair so that a long context is
 // covered by many tiles in flight.  Many pairs (wide batches): 4 warps per block, so that several blocks are resident
 // per SM and the staging / merge phases of one overlap the tile loads of the others.
+// result element -> fp32 vector, or (wide decode path) directly the bf16 hi+lo operand pair of the O-projection GEMM
+__device__ __forceinline__ void attn_store(const AttnDecodeArgs& a, size_t idx, float v) {
+  if (a.out_hi) {
+    const uint16_t h = f32_to_bf16_bits(v);
+    a.out_hi[idx] = h;
+    if (a.out_lo) a.out_lo[idx] = f32_to_bf16_bits(v - __uint_as_float((uint32_t)h << 16));
+  } else {
+    a.out[idx] = v;
+  }
+}
+
 template <int D, int G, typename KVT, int AWARPS>
 __global__ void __launch_bounds__(AWARPS * 32, AWARPS == 4 ? 4 : 1) attn_decode_kernel(const AttnDecodeArgs a) {
   using M = LaneMap<D, G, KVT>;
@@ -131,7 +142,7 @@ __global__ void __launch_bounds__(AWARPS * 32, AWARPS == 4 ? 4 : 1) attn_decode_
     if (a.nsplit == 1) {
       const float inv = 1.0f / L;
 #pragma unroll
-      for (int i = 0; i < DPL; ++i) a.out[(size_t)b * QD + (size_t)head * D + lane * DPL + i] = O[i] * inv;
+      for (int i = 0; i < DPL; ++i) attn_store(a, (size_t)b * QD + (size_t)head * D + lane * DPL + i, O[i] * inv);
     } else {
       float* gp = a.scratch + (((size_t)b * a.q_heads + head) * a.nsplit + split) * PS;
 #pragma unroll
@@ -165,7 +176,7 @@ __global__ void __launch_bounds__(AWARPS * 32, AWARPS == 4 ? 4 : 1) attn_decode_
       L = fmaf(__ldcg(gp + (size_t)sp * PS + D + 1), wt, L);
       O = fmaf(__ldcg(gp + (size_t)sp * PS + i), wt, O);
     }
-    a.out[(size_t)b * QD + (size_t)head * D + i] = O / L;
+    attn_store(a, (size_t)b * QD + (size_t)head * D + i, O / L);
   }
   if (tid == 0) *ctr = 0u;
 }

@@ -238,14 +238,13 @@ int enqueue_wide_step(llmc_engine* e, int B, int nsplit) {
     {
       AttnDecodeArgs a;
       memset(&a, 0, sizeof(a));
-      a.q = e->q; a.out = e->attn; a.kpool = kp; a.vpool = vp; a.kv_fp32 = e->kv_fp32;
+      a.q = e->q; a.out = e->attn; a.out_hi = e->pattn; a.out_lo = e->pattn_lo; a.kpool = kp; a.vpool = vp; a.kv_fp32 = e->kv_fp32;
       a.slots = e->d_slots; a.seq_len = e->d_seq_len; a.ctx_extra = 1;
       a.block_table = e->d_block_table; a.bt_stride = e->pages_per_seq;
       a.page_size = e->page_size; a.q_heads = d.q_heads; a.kv_heads = d.kv_heads; a.head_dim = d.head_dim;
       a.B = B; a.nsplit = nsplit; a.scratch = e->attn_scratch; a.counters = e->attn_counters;
       E_TRY(launch_attn_decode(a, pdl, s));
     }
-    E_TRY(launch_split_rows(e->attn, (size_t)B * QD, e->pattn, e->pattn_lo, s, pdl));
     if (int rc = gemm(e, e->pattn, e->pattn_lo, w.wo, e->px, nullptr, B, H, QD, GEMM_RESID_F32, true)) return rc;
     E_TRY(launch_rmsnorm_rows(e->px, w.g2, d.rms_eps, B, H, e->pxn, e->pxn_lo, s, pdl));
     if (int rc = gemm(e, e->pxn, e->pxn_lo, w.wgu, e->pact, e->pact_lo, B, 2 * I, H, GEMM_SWIGLU_BF16, true)) return rc;
@@ -255,7 +254,7 @@ int enqueue_wide_step(llmc_engine* e, int B, int nsplit) {
   if (int rc = gemm(e, e->pxn, e->pxn_lo, e->lmhead, e->logits, nullptr, B, V, H, GEMM_STORE_F32, true)) return rc;
   E_TRY(launch_argmax_finalise(e->logits, B, V, e->d_slots, e->d_next_token, e->d_seq_len, e->d_out_tokens,
                                MAX_STEPS_PER_CALL, e->d_step_counter, e->lm_counter, e->part_val, e->part_idx, s));
-  e->stats.kernel_launches += (uint64_t)d.layers * 5 + 4;   // the GEMMs count themselves
+  e->stats.kernel_launches += (uint64_t)d.layers * 4 + 4;   // the GEMMs count themselves
   return LLMC_OK;
 }
 
@@ -711,7 +710,7 @@ static int decode_group(llmc_engine* e, const int32_t* slots, int32_t nslots, in
   for (int st = 0; st < nsteps && !mega; ++st) {
     if (ge) {
       E_TRY(cudaGraphLaunch(ge, s));
-      e->stats.kernel_launches += nslots >= e->wide_min_batch ? (uint64_t)d.layers * 9 + 5 : (uint64_t)d.layers * 5 + 1;
+      e->stats.kernel_launches += nslots >= e->wide_min_batch ? (uint64_t)d.layers * 8 + 5 : (uint64_t)d.layers * 5 + 1;
     } else {
       if (int rc = enqueue_decode_step(e, nslots, want_logits, nsplit)) return rc;
     }

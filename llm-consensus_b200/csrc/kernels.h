@@ -72,7 +72,9 @@ inline cudaError_t launch_gemv_any(int epi, int pro, const GemvArgs& a, bool pdl
 // ------------------------------------------------------------------ attn_decode.cu
 struct AttnDecodeArgs {
   const float* q;          // [B][q_heads*head_dim] fp32 (RoPE applied)
-  float* out;              // [B][q_heads*head_dim] fp32
+  float* out;              // [B][q_heads*head_dim] fp32 (used when out_hi == NULL)
+  uint16_t* out_hi;        // optional: write the result as bf16 hi (+ lo if out_lo != NULL) instead of fp32
+  uint16_t* out_lo;
   const void* kpool;       // this layer's pages [page][kv_head][page_size][head_dim], bf16 or fp32
   const void* vpool;
   int kv_fp32;
