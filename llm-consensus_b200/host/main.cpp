@@ -228,15 +228,44 @@ Error initRegistry(const Config& cfg, Registry* reg) {  // main.go:395-415
   };
   for (auto& m : cfg.models) add(m);
   add(cfg.judge);
+  // Device slots are dealt in first-appearance order exactly as a sequential loop would (createProvider advances the
+  // counter only for local models); the engines themselves -- CUDA context, weights, KV pool: about a second each --
+  // are then built concurrently, one thread per model.  The first error in list order is reported, like main.go:406-412.
   int next_device = 0;
-  for (auto& model : needed) {
-    std::shared_ptr<Provider> p;
-    int judge_dev = 0;
+  std::vector<int> slot(needed.size(), 0);
+  for (size_t i = 0; i < needed.size(); ++i) {
+    const std::string& model = needed[i];
+    bool stubbed = false;
+    for (const std::string& st : cfg.stubs) {
+      const size_t eq = st.find('=');
+      if (eq != std::string::npos && st.substr(0, eq) == model) stubbed = true;
+    }
+    std::string base;
+    uint64_t off = 0;
+    splitSeedSuffix(model, &base, &off);
+    auto it = knownModels().find(model);
+    if (it == knownModels().end()) it = knownModels().find(base);
+    const bool local = !stubbed && it != knownModels().end() && it->second == ProviderLocal;
     // the judge runs on GPU 0 (BASELINE.json north star) unless it is also one of the fan-out models
     const bool judge_only = model == cfg.judge && std::find(cfg.models.begin(), cfg.models.end(), model) == cfg.models.end();
-    Error e = createProvider(model, cfg, judge_only ? &judge_dev : &next_device, &p);
-    if (e) return Error::New("initializing provider for " + model + ": " + e.msg);
-    reg->Register(model, p);
+    slot[i] = (local && !judge_only) ? next_device++ : 0;
+  }
+  std::vector<std::shared_ptr<Provider>> made(needed.size());
+  std::vector<Error> errs(needed.size(), Error::Nil());
+  std::vector<std::thread> workers;
+  const bool serial = getenv("LLMC_SERIAL_INIT") != nullptr;   // measurement aid: build the engines one after another
+  for (size_t i = 0; i < needed.size(); ++i) {
+    workers.emplace_back([&, i] {
+      int dev = slot[i];
+      errs[i] = createProvider(needed[i], cfg, &dev, &made[i]);
+    });
+    if (serial) workers.back().join();
+  }
+  for (auto& w : workers)
+    if (w.joinable()) w.join();
+  for (size_t i = 0; i < needed.size(); ++i) {
+    if (errs[i]) return Error::New("initializing provider for " + needed[i] + ": " + errs[i].msg);
+    reg->Register(needed[i], made[i]);
   }
   return Error::Nil();
 }
