@@ -138,6 +138,27 @@ def test_ring_decode_teacher_forced_logits(gpu, name, flags):
     e.close()
 
 
+@pytest.mark.parametrize("flags", [0, 32])
+def test_persistent_decode_long_context(gpu, flags):
+    """Attention phase of the persistent kernels over a long context (2 300 positions: 72 tiles = the 8-way split cap,
+    several tiles per warp, chunked prefill before it), teacher-forced against the oracle."""
+    name = "wide-1b"
+    o, e = make_pair(gpu, name, seed=6, flags=flags, max_ctx=2400, max_slots=1)
+    V = DIMS[name]["vocab"]
+    prompt = np.random.default_rng(21).integers(0, V, 2290)
+    n_new = 10
+    otoks, olog = o.generate(prompt, n_new, want_logits=True)
+    slot = e.seq_alloc()
+    nxt, lg = e.prefill(slot, prompt, want_logits=True)
+    worst = np.abs(lg - olog[0]).max()
+    for s in range(1, n_new):
+        e.set_next_token(slot, otoks[s - 1])
+        out, lg = e.decode([slot], 1, want_logits=True)
+        worst = max(worst, np.abs(lg[0] - olog[s]).max())
+    assert worst <= TOL, "logits max-abs %.3e" % worst
+    e.close()
+
+
 @pytest.mark.parametrize("name", WIDE)
 @pytest.mark.parametrize("chunk", [1, 5, 64])
 def test_ring_decode_free_running_matches_register_kernel(gpu, name, chunk):
