@@ -115,8 +115,8 @@ int llmc_prefill(llmc_engine* e, int32_t slot, const int32_t* tokens, int32_t n,
  * ties) the new pending token.  out_tokens[i*nsteps + s] is the token GENERATED for slot i
  * at step s (the argmax of that step's logits); a provider streams llmc_prefill's
  * *next_token first and then these.  logits (may be NULL) receives [nslots][vocab] of the
- * LAST step.  nslots <= max_slots and nsteps <= 4096 per call; groups of up to 8 sequences share one
- * pass over the weights, larger batches run as consecutive groups of 8. */
+ * LAST step.  nslots <= max_slots and nsteps <= 4096 per call; up to 128 sequences share one pass over the
+ * weights per step, larger batches run as consecutive groups of 128. */
 int llmc_decode(llmc_engine* e, const int32_t* slots, int32_t nslots, int32_t nsteps, int32_t* out_tokens,
                 float* logits);
 
