@@ -302,6 +302,26 @@ __global__ void __launch_bounds__(MW * 32, 1) decode_mega_kernel(const MegaArgs 
             }
           }
         });
+        // K/V tiles of this step's attention were evicted from L2 by the weight stream: request them now, so the two
+        // dependent tile loads of the attention phase cost an L2 trip instead of an HBM trip (as in decode_ring.cu)
+        {
+          const int nsp_pf = min(MEGA_MAX_SPLIT, max(1, (ntiles + a.attn_tiles_per_block - 1) / a.attn_tiles_per_block));
+          if ((int)blockIdx.x < a.kv_heads * nsp_pf) {
+            const int kvh = blockIdx.x % a.kv_heads, split = blockIdx.x / a.kv_heads;
+            constexpr int TILE_LINES = TP * D * (int)sizeof(KVT) / 128;
+            for (int tile = split + nsp_pf * warp; tile < ntiles; tile += nsp_pf * MW) {
+              const int p0 = tile * TP;
+              const int page = bt[p0 / a.page_size];
+              const size_t base = (((size_t)page * a.kv_heads + kvh) * a.page_size + (p0 % a.page_size)) * D;
+              const char* kb = reinterpret_cast<const char*>(kpool + base);
+              const char* vb = reinterpret_cast<const char*>(vpool + base);
+              for (int i = lane; i < TILE_LINES; i += 32) {
+                asm volatile("prefetch.global.L2 [%0];" ::"l"(kb + (size_t)i * 128));
+                asm volatile("prefetch.global.L2 [%0];" ::"l"(vb + (size_t)i * 128));
+              }
+            }
+          }
+        }
         grid_barrier(a.barrier, bar_target, a.trace, tix);
       }
 
