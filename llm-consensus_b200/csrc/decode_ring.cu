@@ -34,7 +34,7 @@ constexpr int RTHREADS = (RW + 1) * 32;
 constexpr int SEG = 2048;              // k elements per warp segment
 constexpr int SLOT_BYTES = 32768;      // 8 row segments of SEG bf16
 constexpr int NSLOT = 6;
-constexpr int RING_MAX_SPLIT = 8;      // = MEGA_MAX_SPLIT: blocks per kv head in the attention phase (scratch layout)
+constexpr int RING_MAX_SPLIT = 16;     // blocks per kv head in the attention phase (scratch layout [kv head][16][G])
 enum { MODE_QKV = 0, MODE_RESID = 1, MODE_SWIGLU = 2, MODE_LMHEAD = 3 };
 
 struct RPhase {
@@ -386,7 +386,11 @@ __global__ void __launch_bounds__(RTHREADS, 1) decode_ring_kernel(const MegaArgs
       const MegaLayer& ly = a.layers[l];
       KVT* kpool = reinterpret_cast<KVT*>(ly.kp);
       KVT* vpool = reinterpret_cast<KVT*>(ly.vp);
-      const int nsp = min(RING_MAX_SPLIT, max(1, (ntiles + a.attn_tiles_per_block - 1) / a.attn_tiles_per_block));
+      const int rec_stride = min(RING_MAX_SPLIT, a.max_tiles);   // split records per kv head in the scratch
+      // splits per kv head: about attn_tiles_per_block tiles per block, bounded by the scratch layout, the scratch
+      // size (max_tiles records per q head) and the number of blocks
+      const int nsp = max(1, min(min(RING_MAX_SPLIT, min(a.max_tiles, grid / a.kv_heads)),
+                                 (ntiles + a.attn_tiles_per_block - 1) / a.attn_tiles_per_block));
 
       // ---------------- P1: RMSNorm -> QKV -> RoPE -> KV append
       {
@@ -496,7 +500,7 @@ __global__ void __launch_bounds__(RTHREADS, 1) decode_ring_kernel(const MegaArgs
 #pragma unroll
               for (int i = 0; i < DPL; ++i) a.attn[(size_t)(kvh * G + h) * D + lane * DPL + i] = O[i] * inv;
             } else {
-              float* rec = a.attn_scratch + (((size_t)kvh * RING_MAX_SPLIT + split) * G + h) * PS;
+              float* rec = a.attn_scratch + (((size_t)kvh * rec_stride + split) * G + h) * PS;
 #pragma unroll
               for (int i = 0; i < DPL; ++i) rec[lane * DPL + i] = O[i];
               if (lane == 0) {
@@ -516,7 +520,7 @@ __global__ void __launch_bounds__(RTHREADS, 1) decode_ring_kernel(const MegaArgs
             __threadfence();
             constexpr int DPL = D / 32;
             const int h = warp;
-            const float* rb = a.attn_scratch + ((size_t)kvh * RING_MAX_SPLIT * G + h) * PS;
+            const float* rb = a.attn_scratch + ((size_t)kvh * rec_stride * G + h) * PS;
             float mv[RING_MAX_SPLIT], lv[RING_MAX_SPLIT], ov[RING_MAX_SPLIT][DPL];
 #pragma unroll
             for (int sp = 0; sp < RING_MAX_SPLIT; ++sp) {
