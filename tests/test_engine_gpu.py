@@ -397,3 +397,32 @@ def test_wide_batch_decode_full_size_1b(gpu):
     print("wide decode, 1B shape, %d sequences: worst last-step logit err %.3e" % (B, worst))
     assert worst <= TOL
     e.close()
+
+
+@pytest.mark.parametrize("flags", [1, 2, 3, 4, 8, 12])   # no graph, no PDL, both, bf16 KV, single-bf16 operands, both
+@pytest.mark.parametrize("B", [5, 40])
+def test_wide_decode_engine_flags(gpu, B, flags):
+    """The wide decode path under every engine flag that changes how its kernels are launched or what they read."""
+    name = "small-d128"
+    V = DIMS[name]["vocab"]
+    e = gpu.Engine(dims=DIMS[name], seed=9, max_ctx=128, max_slots=B, prefill_impl=DEFAULT_IMPL, flags=flags)
+    rng = np.random.default_rng(B + flags)
+    prompts = [rng.integers(0, V, int(n)) for n in rng.integers(3, 50, B)]
+    slots, firsts = [], []
+    for p in prompts:
+        s = e.seq_alloc()
+        slots.append(s)
+        firsts.append(e.prefill(s, p))
+    n_new = 8
+    out, lg = e.decode(slots, n_new, want_logits=True)
+    o = ref.Oracle(name, seed=9, max_ctx=128)
+    tol = TOL if not flags & 12 else 8e-2      # reduced-precision storage modes: see test_reduced_precision_modes
+    for i in range(0, B, max(1, B // 6)):
+        o.reset()
+        otoks, olog = o.generate(prompts[i], n_new + 1, want_logits=True)
+        gt = [firsts[i]] + out[i].tolist()
+        where, margin = greedy_agreement(otoks, olog, gt, tol=tol)
+        assert where < 0, (i, where, margin)
+        if where == -1:
+            assert np.abs(lg[i] - olog[n_new]).max() <= tol
+    e.close()
