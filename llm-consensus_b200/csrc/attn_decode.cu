@@ -94,8 +94,46 @@ __global__ void __launch_bounds__(AWARPS * 32, AWARPS == 4 ? 4 : 1) attn_decode_
   const int* bt = a.block_table + (size_t)slot * a.bt_stride;
   float* pw = pbuf + (size_t)warp * G * (TP + 1);
 
-  for (int i = tid; i < G * D; i += AWARPS * 32) qs[i] = a.q[(size_t)b * QD + (size_t)kvh * G * D + i];
-  __syncthreads();
+  if (a.qkv_raw) {
+    // Wide decode path: the QKV GEMM's raw output [B][(q_heads + 2 kv_heads) * D] comes straight here.  RoPE at this
+    // sequence's position is applied to q while it is staged, and the block that owns the last tile rotates the new
+    // K row and appends it and the V row to the sequence's page before any warp reads that tile (same arithmetic
+    // as rope_append_batch_kernel, which this replaces).
+    constexpr int hd2 = D / 2;
+    const int pos = ctx - 1;
+    const float* raw = a.qkv_raw + (size_t)b * (a.q_heads + 2 * a.kv_heads) * D;
+    const float* rc = a.rope_cos + (size_t)pos * hd2;
+    const float* rs = a.rope_sin + (size_t)pos * hd2;
+    for (int i = tid; i < G * hd2; i += AWARPS * 32) {
+      const int h = i / hd2, j = i - h * hd2;
+      const float* src = raw + (size_t)(kvh * G + h) * D;
+      const float v0 = src[j], v1 = src[j + hd2], cs = rc[j], sn = rs[j];
+      qs[h * D + j] = v0 * cs - v1 * sn;
+      qs[h * D + j + hd2] = v1 * cs + v0 * sn;
+    }
+    if ((ntiles - 1) / per == split) {
+      const int page = bt[pos / a.page_size];
+      const size_t eo = (((size_t)page * a.kv_heads + kvh) * a.page_size + (pos % a.page_size)) * D;
+      KVT* kd = const_cast<KVT*>(kpool) + eo;
+      KVT* vd = const_cast<KVT*>(vpool) + eo;
+      const float* ks = raw + (size_t)(a.q_heads + kvh) * D;
+      const float* vs = raw + (size_t)(a.q_heads + a.kv_heads + kvh) * D;
+      for (int j = tid; j < hd2; j += AWARPS * 32) {
+        const float k0 = ks[j], k1 = ks[j + hd2], cs = rc[j], sn = rs[j];
+        const float r0 = k0 * cs - k1 * sn, r1 = k1 * cs + k0 * sn;
+        if constexpr (sizeof(KVT) == 4) {
+          kd[j] = r0; kd[j + hd2] = r1;
+          vd[j] = vs[j]; vd[j + hd2] = vs[j + hd2];
+        } else {
+          kd[j] = f32_to_bf16_bits(r0); kd[j + hd2] = f32_to_bf16_bits(r1);
+          vd[j] = f32_to_bf16_bits(vs[j]); vd[j + hd2] = f32_to_bf16_bits(vs[j + hd2]);
+        }
+      }
+    }
+  } else {
+    for (int i = tid; i < G * D; i += AWARPS * 32) qs[i] = a.q[(size_t)b * QD + (size_t)kvh * G * D + i];
+  }
+  __syncthreads();   // q staged; the appended K/V row is visible to this block's loads
 
   float m[G], l[G], o[G][EPL];                      // m, l warp-uniform; o: partial over this lane's rows
 #pragma unroll

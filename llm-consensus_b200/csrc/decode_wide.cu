@@ -7,6 +7,7 @@
 //   embed_slots            x[b] = embedding row of next_token[slots[b]]
 //   rope_append_batch      RoPE at position seq_len[slot] of each sequence, K/V appended to that sequence's page
 //   split_rows             fp32 attention output -> bf16 hi+lo GEMM operand
+//                          (both now folded into attn_decode_kernel on the engine's path; kept for the comparator)
 //   argmax_finalise        greedy argmax per row (lowest index on ties), next_token / seq_len / output token
 // All HBM-bound and negligible next to the weight stream.
 //

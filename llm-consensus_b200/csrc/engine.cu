@@ -232,13 +232,10 @@ int enqueue_wide_step(llmc_engine* e, int B, int nsplit) {
     // would cut the chain of programmatic dependent launches)
     E_TRY(launch_rmsnorm_rows(e->px, w.g1, d.rms_eps, B, H, e->pxn, e->pxn_lo, s, pdl, e->pqkv, QD + 2 * KD));
     if (int rc = gemm(e, e->pxn, e->pxn_lo, w.wqkv, e->pqkv, nullptr, B, QD + 2 * KD, H, GEMM_RESID_F32, true)) return rc;
-    E_TRY(launch_rope_append_batch(e->pqkv, B, e->d_slots, e->d_seq_len, e->rope_cos, e->rope_sin, e->d_block_table,
-                                   e->pages_per_seq, kp, vp, e->kv_fp32, e->page_size, d.q_heads, d.kv_heads,
-                                   d.head_dim, e->q, s, pdl));
     {
       AttnDecodeArgs a;
       memset(&a, 0, sizeof(a));
-      a.q = e->q; a.out = e->attn; a.out_hi = e->pattn; a.out_lo = e->pattn_lo; a.kpool = kp; a.vpool = vp; a.kv_fp32 = e->kv_fp32;
+      a.q = e->q; a.qkv_raw = e->pqkv; a.rope_cos = e->rope_cos; a.rope_sin = e->rope_sin; a.out = e->attn; a.out_hi = e->pattn; a.out_lo = e->pattn_lo; a.kpool = kp; a.vpool = vp; a.kv_fp32 = e->kv_fp32;
       a.slots = e->d_slots; a.seq_len = e->d_seq_len; a.ctx_extra = 1;
       a.block_table = e->d_block_table; a.bt_stride = e->pages_per_seq;
       a.page_size = e->page_size; a.q_heads = d.q_heads; a.kv_heads = d.kv_heads; a.head_dim = d.head_dim;
@@ -254,7 +251,7 @@ int enqueue_wide_step(llmc_engine* e, int B, int nsplit) {
   if (int rc = gemm(e, e->pxn, e->pxn_lo, e->lmhead, e->logits, nullptr, B, V, H, GEMM_STORE_F32, true)) return rc;
   E_TRY(launch_argmax_finalise(e->logits, B, V, e->d_slots, e->d_next_token, e->d_seq_len, e->d_out_tokens,
                                MAX_STEPS_PER_CALL, e->d_step_counter, e->lm_counter, e->part_val, e->part_idx, s));
-  e->stats.kernel_launches += (uint64_t)d.layers * 4 + 4;   // the GEMMs count themselves
+  e->stats.kernel_launches += (uint64_t)d.layers * 3 + 4;   // the GEMMs count themselves
   return LLMC_OK;
 }
 
@@ -710,7 +707,7 @@ static int decode_group(llmc_engine* e, const int32_t* slots, int32_t nslots, in
   for (int st = 0; st < nsteps && !mega; ++st) {
     if (ge) {
       E_TRY(cudaGraphLaunch(ge, s));
-      e->stats.kernel_launches += nslots >= e->wide_min_batch ? (uint64_t)d.layers * 8 + 5 : (uint64_t)d.layers * 5 + 1;
+      e->stats.kernel_launches += nslots >= e->wide_min_batch ? (uint64_t)d.layers * 7 + 5 : (uint64_t)d.layers * 5 + 1;
     } else {
       if (int rc = enqueue_decode_step(e, nslots, want_logits, nsplit)) return rc;
     }

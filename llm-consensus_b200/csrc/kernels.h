@@ -71,7 +71,9 @@ inline cudaError_t launch_gemv_any(int epi, int pro, const GemvArgs& a, bool pdl
 
 // ------------------------------------------------------------------ attn_decode.cu
 struct AttnDecodeArgs {
-  const float* q;          // [B][q_heads*head_dim] fp32 (RoPE applied)
+  const float* q;          // [B][q_heads*head_dim] fp32 (RoPE applied); unused when qkv_raw != NULL
+  const float* qkv_raw;    // optional: raw QKV rows [B][(q_heads+2kv_heads)*head_dim]; the kernel then applies RoPE to q
+  const float *rope_cos, *rope_sin;  //   and appends the rotated K row and the V row itself (pools are written)
   float* out;              // [B][q_heads*head_dim] fp32 (used when out_hi == NULL)
   uint16_t* out_hi;        // optional: write the result as bf16 hi (+ lo if out_lo != NULL) instead of fp32
   uint16_t* out_lo;

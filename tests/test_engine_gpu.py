@@ -426,3 +426,30 @@ def test_wide_decode_engine_flags(gpu, B, flags):
         if where == -1:
             assert np.abs(lg[i] - olog[n_new]).max() <= tol
     e.close()
+
+
+def test_wide_decode_long_context_two_attention_blocks(gpu):
+    """Wide path with contexts past 2 048 tokens: the decode attention then runs two blocks per (sequence, kv head);
+    the one that owns the last tile applies RoPE to the new K row and appends K/V itself."""
+    name = "tiny"
+    V = DIMS[name]["vocab"]
+    e = gpu.Engine(dims=DIMS[name], seed=12, max_ctx=2304, max_slots=3, prefill_impl=DEFAULT_IMPL)
+    o = ref.Oracle(name, seed=12, max_ctx=2304)
+    rng = np.random.default_rng(5)
+    prompts = [rng.integers(0, V, n) for n in (2100, 2047, 2200)]
+    slots, firsts = [], []
+    for p in prompts:
+        s = e.seq_alloc()
+        slots.append(s)
+        firsts.append(e.prefill(s, p))
+    n_new = 6
+    out, lg = e.decode(slots, n_new, want_logits=True)
+    for i, p in enumerate(prompts):
+        o.reset()
+        otoks, olog = o.generate(p, n_new + 1, want_logits=True)
+        gt = [firsts[i]] + out[i].tolist()
+        where, margin = greedy_agreement(otoks, olog, gt)
+        assert where < 0, (i, where, margin)
+        if where == -1:
+            assert np.abs(lg[i] - olog[n_new]).max() <= TOL
+    e.close()
