@@ -21,6 +21,8 @@
 // HBM-bound; algorithmic bytes per step as for the other decode paths.
 //
 // No counterpart in the reference (/root/reference/internal/provider/provider.go:13-21 is the boundary).
+#include <type_traits>
+
 #include "attn_tile.cuh"
 #include "common.cuh"
 #include "kernels.h"
@@ -521,32 +523,39 @@ __global__ void __launch_bounds__(RTHREADS, 1) decode_ring_kernel(const MegaArgs
             constexpr int DPL = D / 32;
             const int h = warp;
             const float* rb = a.attn_scratch + ((size_t)kvh * rec_stride * G + h) * PS;
-            float mv[RING_MAX_SPLIT], lv[RING_MAX_SPLIT], ov[RING_MAX_SPLIT][DPL];
+            // all record loads of a lane are issued together (one L2 round trip); the common case of at most 8
+            // splits runs the half-size copy of the code
+            auto merge = [&](auto cap) {
+              constexpr int CAP = decltype(cap)::value;
+              float mv[CAP], lv[CAP], ov[CAP][DPL];
 #pragma unroll
-            for (int sp = 0; sp < RING_MAX_SPLIT; ++sp) {
-              const float* r = rb + (size_t)sp * G * PS;
-              const bool live = sp < nsp;
-              mv[sp] = live ? __ldcg(r + D) : -INFINITY;
-              lv[sp] = live ? __ldcg(r + D + 1) : 0.f;
+              for (int sp = 0; sp < CAP; ++sp) {
+                const float* r = rb + (size_t)sp * G * PS;
+                const bool live = sp < nsp;
+                mv[sp] = live ? __ldcg(r + D) : -INFINITY;
+                lv[sp] = live ? __ldcg(r + D + 1) : 0.f;
 #pragma unroll
-              for (int i = 0; i < DPL; ++i) ov[sp][i] = live ? __ldcg(r + lane * DPL + i) : 0.f;
-            }
-            float M = -INFINITY;
+                for (int i = 0; i < DPL; ++i) ov[sp][i] = live ? __ldcg(r + lane * DPL + i) : 0.f;
+              }
+              float M = -INFINITY;
 #pragma unroll
-            for (int sp = 0; sp < RING_MAX_SPLIT; ++sp) M = fmaxf(M, mv[sp]);
-            float L = 0.f, O[DPL];
+              for (int sp = 0; sp < CAP; ++sp) M = fmaxf(M, mv[sp]);
+              float L = 0.f, O[DPL];
 #pragma unroll
-            for (int i = 0; i < DPL; ++i) O[i] = 0.f;
+              for (int i = 0; i < DPL; ++i) O[i] = 0.f;
 #pragma unroll
-            for (int sp = 0; sp < RING_MAX_SPLIT; ++sp) {
-              const float wt = (mv[sp] == -INFINITY) ? 0.f : __expf(mv[sp] - M);
-              L = fmaf(lv[sp], wt, L);
+              for (int sp = 0; sp < CAP; ++sp) {
+                const float wt = (mv[sp] == -INFINITY) ? 0.f : __expf(mv[sp] - M);
+                L = fmaf(lv[sp], wt, L);
 #pragma unroll
-              for (int i = 0; i < DPL; ++i) O[i] = fmaf(ov[sp][i], wt, O[i]);
-            }
-            const float inv = 1.0f / L;
+                for (int i = 0; i < DPL; ++i) O[i] = fmaf(ov[sp][i], wt, O[i]);
+              }
+              const float inv = 1.0f / L;
 #pragma unroll
-            for (int i = 0; i < DPL; ++i) a.attn[(size_t)(kvh * G + h) * D + lane * DPL + i] = O[i] * inv;
+              for (int i = 0; i < DPL; ++i) a.attn[(size_t)(kvh * G + h) * D + lane * DPL + i] = O[i] * inv;
+            };
+            if (nsp <= 8) merge(std::integral_constant<int, 8>{});
+            else merge(std::integral_constant<int, RING_MAX_SPLIT>{});
             if (lane == 0 && h == 0) a.attn_counters[kvh] = 0u;
           }
         }
