@@ -17,6 +17,7 @@
 //   prefill   x[T][H] fp32, qkv[T][(nq+2nkv)d] fp32, q[T][nq d] fp32; GEMM operands xn[T][H],
 //             attn[T][nq d], act[T][I] as bf16 hi (+ lo) pairs, for T = prefill_chunk
 #include <cuda_runtime.h>
+#include <chrono>
 #include <math.h>
 #include <stdlib.h>
 #include <string.h>
@@ -369,7 +370,16 @@ void llmc_engine_destroy(llmc_engine* e) {
 }
 
 static int create_impl(llmc_engine* e, const llmc_config& c) {
+  const bool init_trace = getenv("LLMC_INIT_TRACE") != nullptr;   // stderr timestamps of the set-up stages
+  const auto init_t0 = std::chrono::steady_clock::now();
+  auto stage = [&](const char* what) {
+    if (init_trace)
+      fprintf(stderr, "[init dev %d] %-18s +%.1f ms\n", c.device, what,
+              std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - init_t0).count());
+  };
   E_TRY(cudaSetDevice(c.device));
+  E_TRY(cudaFree(0));
+  stage("context");
   E_TRY(cudaGetDeviceProperties(&e->prop, c.device));
   if (e->prop.major != 10)
     return fail(e, LLMC_ERR_CUDA, std::string("device ") + e->prop.name + " is compute capability " +
@@ -400,6 +410,8 @@ static int create_impl(llmc_engine* e, const llmc_config& c) {
   E_TRY(cudaEventCreate(&e->ev0));
   E_TRY(cudaEventCreate(&e->ev1));
   if (int rc = init_weights(e, c.weights_path)) return rc;
+  if (init_trace) cudaStreamSynchronize(e->stream);
+  stage("weights");
 
   const ModelDims& d = e->d;
   const int H = d.hidden, QD = d.qd(), KD = d.kd(), I = d.inter, V = d.vocab, D = d.head_dim;
@@ -421,6 +433,7 @@ static int create_impl(llmc_engine* e, const llmc_config& c) {
   if (int rc = dalloc(e, &e->d_next_token, e->max_slots)) return rc;
   E_TRY(cudaMemsetAsync(e->d_seq_len, 0, e->max_slots * sizeof(int), e->stream));
   E_TRY(cudaMemsetAsync(e->d_next_token, 0, e->max_slots * sizeof(int), e->stream));
+  stage("kv pool");
   // ---- RoPE tables (double precision on the host, rounded once to fp32)
   {
     std::vector<float> hc((size_t)e->max_ctx * (D / 2)), hs((size_t)e->max_ctx * (D / 2));
@@ -499,6 +512,7 @@ static int create_impl(llmc_engine* e, const llmc_config& c) {
     if (int rc = dalloc(e, &e->pattn_ws, prefill_attn_mma_workspace_bytes(e->max_ctx, d.kv_heads, d.head_dim) / 2)) return rc;
   E_TRY(cudaStreamSynchronize(e->stream));
   E_TRY(cudaGetLastError());
+  stage("workspaces, sync");
   e->stats.graph_enabled = e->use_graph;
   e->stats.pdl_enabled = e->use_pdl;
   return LLMC_OK;

@@ -231,6 +231,12 @@ Error initRegistry(const Config& cfg, Registry* reg) {  // main.go:395-415
   // Device slots are dealt in first-appearance order exactly as a sequential loop would (createProvider advances the
   // counter only for local models); the engines themselves -- CUDA context, weights, KV pool: about a second each --
   // are then built concurrently, one thread per model.  The first error in list order is reported, like main.go:406-412.
+  if (getenv("LLMC_INIT_TRACE")) {   // how long the CUDA driver itself takes to come up (all GPUs of the node)
+    const auto t0 = std::chrono::steady_clock::now();
+    const int n = llmc_device_count();
+    fprintf(stderr, "[init] CUDA driver up, %d device(s): %.1f ms\n", n,
+            std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count());
+  }
   int next_device = 0;
   std::vector<int> slot(needed.size(), 0);
   for (size_t i = 0; i < needed.size(); ++i) {
