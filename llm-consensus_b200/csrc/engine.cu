@@ -398,6 +398,11 @@ static int create_impl(llmc_engine* e, const llmc_config& c) {
   e->split_prefill = !(c.flags & LLMC_FLAG_PREFILL_BF16);
   e->use_mega = !(c.flags & LLMC_FLAG_NO_MEGAKERNEL);
   {
+    // experiment knob: which prefill GEMMs get the hi+lo activation pair (1 QKV, 2 O, 4 gate/up, 8 down); default all
+    const char* sm = getenv("LLMC_PREFILL_SPLIT_MASK");
+    e->split_mask = sm ? atoi(sm) : 15;
+  }
+  {
     const char* wm = getenv("LLMC_WIDE_MIN_BATCH");   // experiment knob: smallest batch served by the wide (GEMM) decode path
     e->wide_min_batch = wm ? std::max(2, atoi(wm)) : 2;
     if (e->wide_min_batch > MAX_GEMV_BATCH + 1) e->wide_min_batch = MAX_GEMV_BATCH + 1;
@@ -637,16 +642,16 @@ int llmc_prefill(llmc_engine* e, int32_t slot, const int32_t* tokens, int32_t n,
       unsigned char* kp = e->kpool + (size_t)l * e->kv_layer_stride * e->kv_elem;
       unsigned char* vp = e->vpool + (size_t)l * e->kv_layer_stride * e->kv_elem;
       E_TRY(launch_rmsnorm_rows(e->px, w.g1, d.rms_eps, T, H, e->pxn, e->pxn_lo, s));
-      if (int rc = gemm(e, e->pxn, e->pxn_lo, w.wqkv, e->pqkv, nullptr, T, QD + 2 * KD, H, GEMM_STORE_F32)) return rc;
+      if (int rc = gemm(e, e->pxn, (e->split_mask & 1) ? e->pxn_lo : nullptr, w.wqkv, e->pqkv, nullptr, T, QD + 2 * KD, H, GEMM_STORE_F32)) return rc;
       E_TRY(launch_rope_append(e->pqkv, T, p0, slot, e->rope_cos, e->rope_sin, e->d_block_table, e->pages_per_seq,
                                kp, vp, e->kv_fp32, e->page_size, d.q_heads, d.kv_heads, d.head_dim, e->pq, s));
       E_TRY(launch_prefill_attention(e->pq, T, p0, slot, e->d_block_table, e->pages_per_seq, kp, vp, e->kv_fp32,
                                      e->page_size, d.q_heads, d.kv_heads, d.head_dim, e->pattn, e->pattn_lo, e->pattn_ws,
                                      e->prefill_impl, s));
-      if (int rc = gemm(e, e->pattn, e->pattn_lo, w.wo, e->px, nullptr, T, H, QD, GEMM_RESID_F32)) return rc;
+      if (int rc = gemm(e, e->pattn, (e->split_mask & 2) ? e->pattn_lo : nullptr, w.wo, e->px, nullptr, T, H, QD, GEMM_RESID_F32)) return rc;
       E_TRY(launch_rmsnorm_rows(e->px, w.g2, d.rms_eps, T, H, e->pxn, e->pxn_lo, s));
-      if (int rc = gemm(e, e->pxn, e->pxn_lo, w.wgu, e->pact, e->pact_lo, T, 2 * I, H, GEMM_SWIGLU_BF16)) return rc;
-      if (int rc = gemm(e, e->pact, e->pact_lo, w.wd, e->px, nullptr, T, H, I, GEMM_RESID_F32)) return rc;
+      if (int rc = gemm(e, e->pxn, (e->split_mask & 4) ? e->pxn_lo : nullptr, w.wgu, e->pact, e->pact_lo, T, 2 * I, H, GEMM_SWIGLU_BF16)) return rc;
+      if (int rc = gemm(e, e->pact, (e->split_mask & 8) ? e->pact_lo : nullptr, w.wd, e->px, nullptr, T, H, I, GEMM_RESID_F32)) return rc;
     }
     e->stats.kernel_launches += 1 + (uint64_t)d.layers * 4;
   }

@@ -42,6 +42,7 @@ struct llmc_engine {
   size_t kv_layer_stride = 0;                        // elements per layer
   int kv_fp32 = 1, kv_elem = 4;
   bool split_prefill = true;
+  int split_mask = 15;  // LLMC_PREFILL_SPLIT_MASK: which prefill GEMMs take the hi+lo pair (1 QKV, 2 O, 4 gate/up, 8 down)
   int* d_block_table = nullptr;
   std::vector<int> h_block_table;
   std::vector<int> free_pages;
