@@ -50,13 +50,16 @@ __device__ __forceinline__ uint4 ld16(const void* p) {
   else return *reinterpret_cast<const uint4*>(p);
 }
 
-template <int D, int G, typename KVT, bool CG = false>
+// LDF: 16-byte loads in flight per phase (a kernel with registers to spare raises it so that a whole K or V tile is
+// requested at once: one memory round trip per phase instead of two)
+template <int D, int G, typename KVT, bool CG = false, int LDF = LaneMap<D, G, KVT>::LD>
 __device__ __forceinline__ void attn_tile_step(const float* __restrict__ qs, float* __restrict__ pw,
                                                const KVT* __restrict__ kl, const KVT* __restrict__ vl, int valid,
                                                float scale, float (&m)[G], float (&l)[G],
                                                float (&o)[G][LaneMap<D, G, KVT>::EPL]) {
   using M = LaneMap<D, G, KVT>;
-  constexpr int EPV = M::EPV, LPR = M::LPR, CPL = M::CPL, RPP = M::RPP, NP = M::NP, EPL = M::EPL, PPG = M::PPG;
+  constexpr int EPV = M::EPV, LPR = M::LPR, CPL = M::CPL, RPP = M::RPP, NP = M::NP, EPL = M::EPL;
+  constexpr int PPG = (LDF / CPL) < NP ? ((LDF / CPL) < 1 ? 1 : (LDF / CPL)) : NP;
   const int lane = threadIdx.x & 31;
   const int sub = lane / LPR, c = lane % LPR;
     // ---- scores: partial dots over this lane's chunks, reduced over the LPR lanes of a row

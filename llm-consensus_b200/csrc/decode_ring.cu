@@ -8,7 +8,7 @@
 //     and issues `cp.async.bulk` (TMA, 1-D) copies of 32 KB slots into a 6-slot ring, throttled only by the
 //     ring's empty barriers.  Weights never depend on activations, so the producer runs through grid barriers
 //     and through the attention phase: 148 x 192 KB = 28 MB (4 us of HBM time) is always in flight or on chip;
-//   * 8 consumer warps (two groups of 4 that alternate slots) wait on a slot's full barrier, read the rows
+//   * 8 consumer warps (two groups of 4 that alternate slots; the block is 12 warps, see the register note below) wait on a slot's full barrier, read the rows
 //     with conflict-free 16-byte shared loads and multiply with the activation vector they hold in REGISTERS
 //     (a warp owns a 2048-element k segment = 64 registers per lane; with H = 2048 every warp holds the whole
 //     normalised vector and computes the RMS itself, so a phase has no block-level synchronisation at all);
@@ -32,7 +32,7 @@ namespace llmc {
 namespace {
 
 constexpr int RW = 8;                  // consumer warps: two groups of 4
-constexpr int RTHREADS = (RW + 1) * 32;
+constexpr int RTHREADS = (RW + 4) * 32;   // two consumer warpgroups + one producer warpgroup (one warp of it works)
 constexpr int SEG = 2048;              // k elements per warp segment
 constexpr int SLOT_BYTES = 32768;      // 8 row segments of SEG bf16
 constexpr int NSLOT = 6;
@@ -150,8 +150,12 @@ __global__ void __launch_bounds__(RTHREADS, 1) decode_ring_kernel(const MegaArgs
   };
 
   // ======================================================================== producer
-  if (warp == RW) {
-    if (lane != 0) return;
+  // Register budget: 9 warps would put three on one scheduler and cap every thread at 168 registers.  With a full
+  // third warpgroup the producer side hands its registers back (setmaxnreg needs whole warpgroups) and the eight
+  // consumer warps get 232 each, which the attention phase uses to request a whole K / V tile at once.
+  if (warp >= RW) {
+    asm volatile("setmaxnreg.dec.sync.aligned.u32 24;");
+    if (warp != RW || lane != 0) return;
     unsigned seq = 0;
     int rot = 0;
     const bool stats = a.trace && blockIdx.x == 0;
@@ -196,6 +200,7 @@ __global__ void __launch_bounds__(RTHREADS, 1) decode_ring_kernel(const MegaArgs
   }
 
   // ======================================================================== consumers
+  asm volatile("setmaxnreg.inc.sync.aligned.u32 232;");
   const int group = warp >> 2, wg = warp & 3;
   unsigned seq = 0;
   int rot = 0;
@@ -472,7 +477,7 @@ __global__ void __launch_bounds__(RTHREADS, 1) decode_ring_kernel(const MegaArgs
             const int valid = min(TP, ctx - p0);
             const int page = bt[p0 / a.page_size];
             const size_t base = (((size_t)page * a.kv_heads + kvh) * a.page_size + (p0 % a.page_size)) * D;
-            attn_tile_step<D, G, KVT, true>(qs, pw, kpool + base + c * LM::EPV, vpool + base + c * LM::EPV, valid,
+            attn_tile_step<D, G, KVT, true, 16>(qs, pw, kpool + base + c * LM::EPV, vpool + base + c * LM::EPV, valid,
                                             scale, m, lsum, o);
           }
           attn_write_record<D, G, KVT>(part + (size_t)warp * G * PS, m, lsum, o);
