@@ -222,11 +222,23 @@ __global__ void __launch_bounds__(RTHREADS, 1) decode_ring_kernel(const MegaArgs
     cbar();
     if (tid == 0) {
       if (a.trace && blockIdx.x == 0) a.trace[2 * tix] = gtime();
+      // LLMC_MEGA_TRACE: every block's arrival time at the barriers of the second step's layer 1 (5 barriers), to
+      // see how far apart the blocks finish a phase
+      if (a.trace && a.nsteps > 1 && tix >= (5 * a.L + 1) + 5 && tix < (5 * a.L + 1) + 10)
+        a.trace[(size_t)2 * (5 * a.L + 1) * a.nsteps + 16 + (size_t)(tix - (5 * a.L + 1) - 5) * gridDim.x + blockIdx.x] = gtime();
       asm volatile("red.release.gpu.global.add.u32 [%0], 1;" ::"l"(a.barrier) : "memory");
       unsigned v;
-      do {
+      if (a.ring_poll_mode == 1) {          // relaxed spin, one acquire load once the count is there (default: the
+                                            // acquire-load spin costs 0.5 % of the step; LLMC_RING_POLL=0 selects it)
+        do {
+          asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(a.barrier) : "memory");
+        } while (v < bar_target);
         asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(a.barrier) : "memory");
-      } while (v < bar_target);
+      } else {
+        do {
+          asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(a.barrier) : "memory");
+        } while (v < bar_target);
+      }
       if (a.trace && blockIdx.x == 0) a.trace[2 * tix + 1] = gtime();
     }
     cbar();

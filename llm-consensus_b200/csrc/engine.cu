@@ -496,7 +496,7 @@ static int create_impl(llmc_engine* e, const llmc_config& c) {
     if (int rc = dalloc(e, &e->mega_barrier, 1)) return rc;
     if (int rc = dalloc(e, &e->mega_counters, (size_t)d.kv_heads)) return rc;
     if (getenv("LLMC_MEGA_TRACE"))
-      if (int rc = dalloc(e, &e->mega_trace, (size_t)2 * (5 * d.layers + 1) * 64 + 16)) return rc;
+      if (int rc = dalloc(e, &e->mega_trace, (size_t)2 * (5 * d.layers + 1) * 64 + 16 + 5 * 256)) return rc;
     E_TRY(cudaMemsetAsync(e->mega_counters, 0, (size_t)d.kv_heads * sizeof(unsigned), e->stream));
   }
   // ---- prefill workspace
@@ -717,6 +717,10 @@ static int decode_group(llmc_engine* e, const int32_t* slots, int32_t nslots, in
       const char* tpb = getenv("LLMC_MEGA_TILES_PER_BLOCK");
       m.attn_tiles_per_block = tpb ? std::max(1, atoi(tpb)) : 4;
     }
+    {
+      const char* pm = getenv("LLMC_RING_POLL");
+      m.ring_poll_mode = pm ? atoi(pm) : 1;
+    }
     m.trace = (e->mega_trace && nsteps <= 64) ? e->mega_trace : nullptr;
     E_TRY(cudaMemsetAsync(e->mega_barrier, 0, sizeof(unsigned), s));
     if (e->use_ring) E_TRY(launch_decode_ring(m, e->prop.multiProcessorCount, s));
@@ -743,7 +747,7 @@ static int decode_group(llmc_engine* e, const int32_t* slots, int32_t nslots, in
   if (mega && e->mega_trace && nsteps <= 64) {
     // debug trace: average per-phase time (barrier open -> next barrier open) and barrier wait of block 0
     const int nb = (5 * d.layers + 1) * nsteps;
-    std::vector<unsigned long long> t((size_t)2 * nb + 16);
+    std::vector<unsigned long long> t((size_t)2 * nb + 16 + 5 * 256);
     E_TRY(cudaMemcpy(t.data(), e->mega_trace, t.size() * sizeof(unsigned long long), cudaMemcpyDeviceToHost));
     const char* names[6] = {"qkv", "attn", "o", "gateup", "down", "lmhead"};
     double phase[6] = {0, 0, 0, 0, 0, 0}, wait[6] = {0, 0, 0, 0, 0, 0};
@@ -760,6 +764,18 @@ static int decode_group(llmc_engine* e, const int32_t* slots, int32_t nslots, in
                           phase[k] / cnt[k] / 1e3, wait[k] / cnt[k] / 1e3, cnt[k]);
     if (e->use_ring) {
       const unsigned long long* st = t.data() + (size_t)2 * nb;
+      if (nsteps > 1) {
+        const int G = e->prop.multiProcessorCount;
+        const char* pn[5] = {"qkv", "attn", "o", "gateup", "down"};
+        for (int k = 0; k < 5; ++k) {
+          std::vector<unsigned long long> v(st + 16 + (size_t)k * G, st + 16 + (size_t)(k + 1) * G);
+          std::sort(v.begin(), v.end());
+          const double last = (double)v[G - 1];
+          fprintf(stderr, "[ring arrivals] %-6s barrier of step 1 layer 1: first block %.2f us before the last, 10%% %.2f, median %.2f, "
+                          "90%% %.2f, second-to-last %.2f\n", pn[k], (last - v[0]) / 1e3, (last - v[G / 10]) / 1e3,
+                  (last - v[G / 2]) / 1e3, (last - v[G * 9 / 10]) / 1e3, (last - v[G - 2]) / 1e3);
+        }
+      }
       fprintf(stderr, "[ring stats] block 0 warp 0, cycles: total %llu = wait-full %llu + x-load %llu + slots %llu (%llu slots seen) "
                       "+ grid barriers %llu; producer: total %llu, wait-empty %llu, %llu slots\n",
               st[4], st[0], st[1], st[2], st[5], st[3], st[9], st[8], st[10]);

@@ -124,6 +124,7 @@ struct MegaArgs {
   unsigned long long* trace;   // nullable: per-barrier (arrive, open) times of block 0, ns
   int attn_tiles_per_block;    // attention: tiles per (kv head, split) block; splits = ceil(tiles / this), <= 8
   int smem_x;                  // filled by the launcher
+  int ring_poll_mode;          // decode_ring grid barrier: 1 (default) relaxed spin + one acquire load, 0 acquire-load spin
 };
 cudaError_t launch_decode_mega(const MegaArgs& a, int sm_count, cudaStream_t s);
 // ------------------------------------------------------------------ decode_ring.cu
