@@ -123,10 +123,11 @@ __device__ __forceinline__ void grid_barrier(unsigned* bar, unsigned& target, un
     // release-add / acquire-poll at gpu scope: the block's writes (ordered before this thread by the
     // barrier above) become visible to every block that observes the count, without a full membar
     asm volatile("red.release.gpu.global.add.u32 [%0], 1;" ::"l"(bar) : "memory");
-    unsigned v;
+    unsigned v;   // relaxed spin, then one acquire load (cheaper than spinning on acquire loads; see decode_ring.cu)
     do {
-      asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(bar) : "memory");
+      asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(bar) : "memory");
     } while (v < target);
+    asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(bar) : "memory");
     if (trace && blockIdx.x == 0) trace[2 * tix + 1] = gtime();
   }
   __syncthreads();
