@@ -8,15 +8,18 @@
 //     and issues `cp.async.bulk` (TMA, 1-D) copies of 32 KB slots into a 6-slot ring, throttled only by the
 //     ring's empty barriers.  Weights never depend on activations, so the producer runs through grid barriers
 //     and through the attention phase: 148 x 192 KB = 28 MB (4 us of HBM time) is always in flight or on chip;
-//   * 8 consumer warps (two groups of 4 that alternate slots; the block is 12 warps, see the register note below) wait on a slot's full barrier, read the rows
-//     with conflict-free 16-byte shared loads and multiply with the activation vector they hold in REGISTERS
-//     (a warp owns a 2048-element k segment = 64 registers per lane; with H = 2048 every warp holds the whole
-//     normalised vector and computes the RMS itself, so a phase has no block-level synchronisation at all);
+//   * 8 consumer warps (two groups of 4 that alternate slots) wait on a slot's full barrier, read the rows with
+//     conflict-free 16-byte shared loads and multiply with the activation vector they hold in REGISTERS (a warp
+//     owns a 2048-element k segment = 64 registers per lane).  The block reads the vector from L2 once per phase
+//     and redistributes it through shared memory, RMSNorm statistics included;
+//   * the block is three full warpgroups (8 consumer warps, 4 producer-side warps of which one thread works), so
+//     that setmaxnreg can hand the producer side's registers to the consumers (24 / 232 per thread);
 //   * a slot is 8 row segments: 4 row pairs (RoPE pairs / gate-up pairs / adjacent rows) when K = 2048, 2 when
 //     K = 4096, 1 pair split over 4 warps when K = 8192.  Slots are dealt round-robin to the blocks with a
 //     rotation that continues across phases, so the per-block byte count is balanced over a layer;
 //   * activations cross SMs through L2 and phases are separated by the same grid barrier as in decode_mega.cu;
-//     the attention phase is that kernel's (block = (kv head, split), warps = 32-position tiles).
+//     the attention phase is that kernel's (block = (kv head, split), warps = 32-position tiles), with up to 16
+//     splits per kv head and the step's K/V tiles requested into L2 before the QKV barrier.
 // Shapes: H = 2048, QD and I in {2048, 4096, 8192} (llama-3.2-1b); other shapes keep decode_mega.cu.
 // HBM-bound; algorithmic bytes per step as for the other decode paths.
 //
