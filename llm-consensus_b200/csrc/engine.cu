@@ -410,6 +410,14 @@ static int create_impl(llmc_engine* e, const llmc_config& c) {
   e->use_ring = e->use_mega && !(c.flags & LLMC_FLAG_NO_RING) &&
                 decode_ring_supported(e->d.hidden, e->d.qd(), e->d.kd(), e->d.inter, e->d.vocab, e->d.q_heads, e->d.kv_heads,
                                       e->d.head_dim);
+  {
+    // LLMC_FLAG_RING_BARRIERS (or LLMC_RING_FLOW=0) keeps the grid-barrier version of the ring kernel
+    const char* fl = getenv("LLMC_RING_FLOW");
+    const bool want_flow = fl ? atoi(fl) != 0 : !(c.flags & LLMC_FLAG_RING_BARRIERS);
+    e->use_flow = e->use_ring && want_flow &&
+                  decode_flow_supported(e->d.hidden, e->d.qd(), e->d.kd(), e->d.inter, e->d.vocab, e->d.q_heads,
+                                        e->d.kv_heads, e->d.head_dim, e->prop.multiProcessorCount);
+  }
   e->stats.sm_count = e->prop.multiProcessorCount; e->stats.cc_major = e->prop.major; e->stats.cc_minor = e->prop.minor;
   E_TRY(cudaStreamCreateWithFlags(&e->stream, cudaStreamNonBlocking));
   E_TRY(cudaEventCreate(&e->ev0));
@@ -498,6 +506,11 @@ static int create_impl(llmc_engine* e, const llmc_config& c) {
     if (getenv("LLMC_MEGA_TRACE"))
       if (int rc = dalloc(e, &e->mega_trace, (size_t)2 * (5 * d.layers + 1) * 64 + 16 + 5 * 256)) return rc;
     E_TRY(cudaMemsetAsync(e->mega_counters, 0, (size_t)d.kv_heads * sizeof(unsigned), e->stream));
+    if (e->use_flow) {
+      e->flow_nwords = decode_flow_words(H, QD, KD, I, d.q_heads, d.kv_heads, D, e->prop.multiProcessorCount);
+      if (int rc = dalloc(e, &e->flow_words, e->flow_nwords)) return rc;
+      E_TRY(cudaMemsetAsync(e->flow_words, 0, e->flow_nwords * sizeof(unsigned long long), e->stream));
+    }
   }
   // ---- prefill workspace
   const int TC = std::max(e->prefill_chunk, WB);   // the wide decode path borrows these buffers (rows = sequences)
@@ -723,7 +736,20 @@ static int decode_group(llmc_engine* e, const int32_t* slots, int32_t nslots, in
     }
     m.trace = (e->mega_trace && nsteps <= 64) ? e->mega_trace : nullptr;
     E_TRY(cudaMemsetAsync(e->mega_barrier, 0, sizeof(unsigned), s));
-    if (e->use_ring) E_TRY(launch_decode_ring(m, e->prop.multiProcessorCount, s));
+    if (e->use_flow) {
+      // hand-over tags continue from launch to launch, so a word left by an earlier call never matches
+      const unsigned need = (unsigned)nsteps * (unsigned)(5 * d.layers + 1);
+      if (e->flow_tag > 0xF0000000u - need) {   // before the 32-bit tags wrap: clear the words, restart at 1
+        E_TRY(cudaMemsetAsync(e->flow_words, 0, e->flow_nwords * sizeof(unsigned long long), s));
+        e->flow_tag = 1;
+      }
+      m.tw = e->flow_words;
+      m.tag0 = e->flow_tag;
+      e->flow_tag += need;
+      const char* fp = getenv("LLMC_FLOW_POLL");
+      m.flow_poll_mode = fp ? atoi(fp) : 0;
+      E_TRY(launch_decode_flow(m, e->prop.multiProcessorCount, s));
+    } else if (e->use_ring) E_TRY(launch_decode_ring(m, e->prop.multiProcessorCount, s));
     else E_TRY(launch_decode_mega(m, e->prop.multiProcessorCount, s));
     e->stats.kernel_launches += 1;
   }
@@ -762,7 +788,7 @@ static int decode_group(llmc_engine* e, const int32_t* slots, int32_t nslots, in
     for (int k = 0; k < 6; ++k)
       if (cnt[k]) fprintf(stderr, "[mega trace] %-7s phase %.2f us (block 0 waited %.2f us at its barrier) x%d\n", names[k],
                           phase[k] / cnt[k] / 1e3, wait[k] / cnt[k] / 1e3, cnt[k]);
-    if (e->use_ring) {
+    if (e->use_ring && !e->use_flow) {
       const unsigned long long* st = t.data() + (size_t)2 * nb;
       if (nsteps > 1) {
         const int G = e->prop.multiProcessorCount;

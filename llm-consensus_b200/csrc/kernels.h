@@ -125,12 +125,22 @@ struct MegaArgs {
   int attn_tiles_per_block;    // attention: tiles per (kv head, split) block; splits = ceil(tiles / this), <= 8
   int smem_x;                  // filled by the launcher
   int ring_poll_mode;          // decode_ring grid barrier: 1 (default) relaxed spin + one acquire load, 0 acquire-load spin
+  // decode_flow.cu only: activations cross SMs as (value, tag) words, no grid barrier
+  unsigned long long* tw;      // decode_flow_words() 8-byte words, zero before the first launch
+  unsigned tag0;               // first tag of this launch (>= 1); the launch uses nsteps * (5 L + 1) consecutive tags
+  int flow_poll_mode;          // 0: one lane per warp watches the first word, then the warp reads; 1: every thread polls
 };
 cudaError_t launch_decode_mega(const MegaArgs& a, int sm_count, cudaStream_t s);
 // ------------------------------------------------------------------ decode_ring.cu
 // same contract as launch_decode_mega; weights travel through a per-SM shared-memory ring filled by TMA bulk copies
 bool decode_ring_supported(int H, int QD, int KD, int I, int V, int q_heads, int kv_heads, int head_dim);
 cudaError_t launch_decode_ring(const MegaArgs& a, int sm_count, cudaStream_t s);
+// ------------------------------------------------------------------ decode_flow.cu
+// the ring kernel without grid barriers: every activation travels as an 8-byte (value, tag) word that its readers
+// poll, so a phase hand-over costs one store-to-load trip through L2 instead of fence + arrive + poll + reload
+bool decode_flow_supported(int H, int QD, int KD, int I, int V, int q_heads, int kv_heads, int head_dim, int sm_count);
+size_t decode_flow_words(int H, int QD, int KD, int I, int q_heads, int kv_heads, int head_dim, int sm_count);
+cudaError_t launch_decode_flow(const MegaArgs& a, int sm_count, cudaStream_t s);
 
 // ------------------------------------------------------------------ prefill.cu
 cudaError_t launch_embed_rows(const uint16_t* emb, const int* tokens, int T, int H, float* x, cudaStream_t s);
