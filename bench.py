@@ -94,16 +94,39 @@ def cpu_sample(threads_all=True, prompt_len=128, new_tokens=64, steps=3, warmup=
                       % (prompt_len, new_tokens, len(times), dt)}, dt / len(times)
 
 
+OURS_CONFIG = {"workload": "local provider query, Llama-3.2-1B shape random-init bf16, 512-token prompt + 256 greedy "
+                           "tokens, batch 1 per GPU (BASELINE.json configs[1]); one model instance (seed = rank) per GPU, "
+                           "no collective",
+               "shape": "llama-3.2-1b", "prompt": PROMPT_LEN, "new_tokens": NEW_TOKENS, "batch": 1}
+
+
 def run_reference(args, rank, world):
+    """The reference arm: the CPU implementation of the same path (the fp32 oracle port: the reference repository has no
+    local inference and Go is not installed) on all host threads.  It runs EXACTLY --steps timed and --warmup untimed
+    steps; each step is a bounded sample of the 512 + 256 workload (same shape, same 2:1 prompt/decode ratio), sized
+    from the first step's time so that the whole run stays within a few minutes."""
     if rank != 0:
         return
-    base, ms = cpu_sample(steps=max(1, min(args.steps, 8)), warmup=min(args.warmup, 1))
+    steps, warmup = max(1, args.steps), max(0, args.warmup)
+    budget_s = 240.0
+    # probe: one 1/16-scale step tells how fast this host is (its cost is ~1/16 of a quarter-scale step's)
+    probe, probe_ms = cpu_sample(prompt_len=32, new_tokens=16, steps=1)
+    per_token_s = probe_ms / (32 + 16)
+    scale = 4
+    for cand in (1, 2, 4, 8, 16):   # the largest sample (smallest divisor) that fits the budget
+        if per_token_s * (PROMPT_LEN + NEW_TOKENS) / cand * (steps + warmup) * 1.3 <= budget_s:
+            scale = cand
+            break
+    else:
+        scale = 16
+    pl, nt = PROMPT_LEN // scale, NEW_TOKENS // scale
+    base, ms = cpu_sample(prompt_len=pl, new_tokens=nt, steps=steps, warmup=warmup)
     line = {"impl": "reference", "metric": METRIC, "value": base["value"], "unit": "tok/s", "n_gpus": args.gpus,
-            "steps": args.steps, "warmup": min(args.warmup, 1), "ms_per_step": ms * 1e3, "higher_is_better": True,
+            "steps": steps, "warmup": warmup, "ms_per_step": ms * 1e3, "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": "local provider query, Llama-3.2-1B shape random-init, 512-token prompt + 256 greedy "
-                                   "tokens (BASELINE.json configs[1]); CPU arm runs a 1/4-scale sample (128 + 64 tokens) per step",
-                       "shape": "llama-3.2-1b", "prompt": PROMPT_LEN, "new_tokens": NEW_TOKENS, "batch": 1},
+            "config": dict(OURS_CONFIG),
+            "sample": "each CPU step is a 1/%d-scale sample of the configured workload: %d-token prompt + %d greedy tokens"
+                      % (scale, pl, nt),
             "cpu_baseline": base,
             "e2e": {"value": base["value"], "unit": "tok/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0,
@@ -112,34 +135,123 @@ def run_reference(args, rank, world):
     print(json.dumps(line), flush=True)
 
 
+class Ranks:
+    """The cross-rank plumbing of the N > 1 run: a barrier, a max and a sum over ranks (torch.distributed; NCCL on the
+    GPU box, gloo in the CPU test).  The measured path itself has no collective."""
+
+    def __init__(self, world, local_rank=0, backend="nccl"):
+        self.world, self.dist, self.device = world, None, "cpu"
+        if world > 1:
+            import torch
+            import torch.distributed as dist
+            if backend == "nccl":
+                torch.cuda.set_device(local_rank)
+                dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+                self.device = "cuda"
+            else:
+                dist.init_process_group(backend)
+            self.dist = dist
+
+    def barrier(self):
+        if self.dist is not None:
+            self.dist.barrier()
+
+    def _reduce(self, v, op):
+        if self.dist is None:
+            return float(v)
+        import torch
+        t = torch.tensor([v], dtype=torch.float64, device=self.device)
+        self.dist.all_reduce(t, op=getattr(self.dist.ReduceOp, op))
+        return float(t.item())
+
+    def allmax(self, v):
+        return self._reduce(v, "MAX")
+
+    def allsum(self, v):
+        return self._reduce(v, "SUM")
+
+    def close(self):
+        if self.dist is not None:
+            self.dist.destroy_process_group()
+
+
+def aggregate(ranks, dev_pre_ms, dev_dec_ms, wall_s, launches, steps, new_tokens=NEW_TOKENS):
+    """Whole-job numbers from this rank's timings: times are the MAX over ranks, work is the SUM over ranks."""
+    dev_ms = ranks.allmax(dev_pre_ms + dev_dec_ms)
+    out = {"dev_ms": dev_ms, "wall_s": ranks.allmax(wall_s), "dec_ms": ranks.allmax(dev_dec_ms),
+           "pre_ms": ranks.allmax(dev_pre_ms), "launches_all": ranks.allsum(float(launches)),
+           "tokens_all": new_tokens * steps * ranks.world}
+    out["value"] = out["tokens_all"] / (dev_ms / 1e3)
+    out["e2e"] = out["tokens_all"] / out["wall_s"]
+    return out
+
+
+def consensus_leg(n_gpus, passes=3):
+    """BASELINE.json's first metric, consensus runs/sec, on config 3: 8 seeds of the 1B shape fanned out over the
+    first n_gpus GPUs (model i -> GPU i mod n_gpus), judge = model 0's instance on GPU 0 over the rendered template,
+    through the CLI mirror of /root/reference/cmd/llm-consensus/main.go:132-163 (fan-out, then judge)."""
+    import re
+    import tempfile
+    cli = os.path.join(ROOT, "llm-consensus_b200", "bin", "llm-consensus")
+    if not os.path.exists(cli):
+        return {"error": "CLI not built"}
+    words = "the quick brown fox jumps over the lazy dog while consensus is computed on eight accelerators "
+    prompt = (words * (PROMPT_LEN // len(words) + 1))[:PROMPT_LEN - 1] + "?"
+    models = ",".join("local-llama-1b-s%d" % i for i in range(8))
+    with tempfile.TemporaryDirectory() as td:
+        pf, out = os.path.join(td, "prompt.txt"), os.path.join(td, "result.json")
+        open(pf, "w").write(prompt)
+        cmd = [cli, "--models", models, "--judge", "local-llama-1b-s0", "--file", pf, "--output", out,
+               "--max-new-tokens", str(NEW_TOKENS), "--max-ctx", "8192", "--timeout", "600", "--quiet"]
+        env = dict(os.environ, LLMC_BENCH_REPEAT=str(passes), CUDA_VISIBLE_DEVICES=",".join(str(i) for i in range(n_gpus)))
+        try:
+            r = subprocess.run(cmd, env=env, capture_output=True, text=True, timeout=600)
+        except subprocess.TimeoutExpired:
+            return {"error": "CLI timed out"}
+        if r.returncode != 0:
+            return {"error": "CLI rc=%d: %s" % (r.returncode, (r.stderr or r.stdout)[-300:])}
+        runs = [float(m.group(1)) for m in re.finditer(r"run ([0-9.]+) ms", r.stderr)]
+        fans = [float(m.group(1)) for m in re.finditer(r"fan-out ([0-9.]+) ms", r.stderr)]
+        judges = [float(m.group(1)) for m in re.finditer(r"judge ([0-9.]+) ms", r.stderr)]
+        doc = json.load(open(out))
+    steady = runs[1:] or runs
+    k = len(runs) - len(steady)
+    return {"consensus_runs_per_s": len(steady) / (sum(steady) / 1e3), "fanout_ms": sum(fans[k:]) / len(fans[k:]),
+            "judge_ms": sum(judges[k:]) / len(judges[k:]), "passes": len(runs), "responses": len(doc["responses"]),
+            "config": "BASELINE.json configs[2]: 8 seeds of the Llama-3.2-1B shape over %d GPU(s), 512-char prompt, %d new "
+                      "tokens each, judge = model 0 on GPU 0; wall clock inside the CLI, first pass dropped" % (n_gpus, NEW_TOKENS)}
+
+
+def decode_8b_leg(llmc, device, peak):
+    """Batch-1 decode of the 8B shape (BASELINE.json configs[3]'s model), 512-token prompt, 128 steps: ms per step and
+    the fraction of the HBM roof on SURVEY section 8(d)'s bytes."""
+    try:
+        eng = llmc.Engine(shape=llmc.SHAPE_LLAMA_8B, device=device, seed=0, max_ctx=1024, max_slots=1)
+    except Exception as ex:   # e.g. not enough free memory next to another tenant
+        return {"error": str(ex)[:200]}
+    prompt = np.random.default_rng(2).integers(0, 128256, PROMPT_LEN).astype(np.int32)
+    slot = eng.seq_alloc()
+    eng.prefill(slot, prompt)
+    pre = eng.stats()["last_prefill_ms"]
+    eng.decode([slot], 8)
+    ms, steps = 0.0, 0
+    for _ in range(2):
+        eng.decode([slot], 64)
+        ms += eng.stats()["last_decode_ms"]
+        steps += 64
+    st = eng.stats()
+    eng.close()
+    ctx = PROMPT_LEN + 8 + steps / 2.0
+    algo = st["weight_bytes"] + (ctx + 1) * 131072.0     # SURVEY 8(d): kv_tok = 128 KiB for the 8B shape
+    step_ms = ms / steps
+    return {"ms_per_step": step_ms, "tok_s": 1e3 / step_ms, "prefill_ms_512": pre,
+            "roofline_frac": algo / (step_ms / 1e3) / 1e9 / peak, "algorithmic_bytes_per_step": algo}
+
+
 def run_ours(args, rank, world, local_rank):
     import llm_consensus_b200.llmc as llmc
-    dist = None
-    if world > 1:
-        import torch
-        import torch.distributed as dist
-        torch.cuda.set_device(local_rank)
-        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
-
-    def barrier():
-        if dist is not None:
-            dist.barrier()
-
-    def allmax(v):
-        if dist is None:
-            return v
-        import torch
-        t = torch.tensor([v], dtype=torch.float64, device="cuda")
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        return float(t.item())
-
-    def allsum(v):
-        if dist is None:
-            return v
-        import torch
-        t = torch.tensor([v], dtype=torch.float64, device="cuda")
-        dist.all_reduce(t, op=dist.ReduceOp.SUM)
-        return float(t.item())
+    ranks = Ranks(world, local_rank, "nccl")
+    barrier = ranks.barrier
 
     if llmc.device_count() < 1:
         raise SystemExit("bench.py: no CUDA device -- libllmc has no CPU fallback")
@@ -178,14 +290,9 @@ def run_ours(args, rank, world, local_rank):
     launches = eng.stats()["kernel_launches"] - launches0
     st = eng.stats()
 
-    dev_ms = allmax(dev_pre + dev_dec)          # device time (CUDA events on the engine's stream), max over ranks
-    wall_s = allmax(wall)
-    dec_ms = allmax(dev_dec)
-    pre_ms = allmax(dev_pre)
-    launches_all = allsum(float(launches))
-    tokens_all = NEW_TOKENS * args.steps * world
-    value = tokens_all / (dev_ms / 1e3)
-    e2e = tokens_all / wall_s
+    agg = aggregate(ranks, dev_pre, dev_dec, wall, launches, args.steps)   # device time: CUDA events on the engine's stream
+    dev_ms, wall_s, dec_ms, pre_ms = agg["dev_ms"], agg["wall_s"], agg["dec_ms"], agg["pre_ms"]
+    launches_all, tokens_all, value, e2e = agg["launches_all"], agg["tokens_all"], agg["value"], agg["e2e"]
     # roofline of the decode step (one pass of the persistent kernel over all weights): algorithmic bytes / device time
     steps_dec = (NEW_TOKENS - 1) * args.steps
     avg_ctx = PROMPT_LEN + (NEW_TOKENS - 1) / 2.0
@@ -201,13 +308,10 @@ def run_ours(args, rank, world, local_rank):
         "metric": METRIC, "value": value, "unit": "tok/s", "n_gpus": world, "steps": args.steps,
         "warmup": max(args.warmup, 3), "ms_per_step": dev_ms / args.steps, "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
-        "config": {"workload": "local provider query, Llama-3.2-1B shape random-init bf16, 512-token prompt + 256 greedy "
-                               "tokens, batch 1 per GPU (BASELINE.json configs[1]); one model instance (seed = rank) per GPU, "
-                               "no collective",
-                   "shape": "llama-3.2-1b", "prompt": PROMPT_LEN, "new_tokens": NEW_TOKENS, "batch": 1,
-                   "l2": "no flush needed: each decode step streams 2.47 GB of weights, 20x the 126 MB L2",
-                   "decode_path": "persistent cooperative kernel, weights through a TMA-fed shared-memory ring (batch 1)", "kv_cache": "fp32",
-                   "prefill_operands": "bf16 hi+lo pairs"},
+        "config": dict(OURS_CONFIG,
+                       l2="no flush needed: each decode step streams 2.47 GB of weights, 20x the 126 MB L2",
+                       decode_path="persistent cooperative kernel, weights through a TMA-fed shared-memory ring (batch 1)",
+                       kv_cache="fp32", prefill_operands="bf16 hi+lo pairs"),
         "decode_only_tok_s_per_gpu": steps_dec / (dec_ms / 1e3),
         "prefill_ms": pre_ms / args.steps,
         "queries_per_s": args.steps * world / (dev_ms / 1e3),
@@ -225,13 +329,20 @@ def run_ours(args, rank, world, local_rank):
                      "algorithmic_bytes_per_launch": bytes_per_step, "avg_launch_us": step_s * 1e6},
         "clocks": clocks,
     }
+    eng.close()
+    barrier()
+    if rank == 0 and not args.no_extra:
+        # extra legs, outside the timed region (other ranks have released their GPUs at the barrier above)
+        line["decode_8b"] = decode_8b_leg(llmc, local_rank, peak)
+        line["consensus"] = consensus_leg(world)
+        for k in ("consensus_runs_per_s", "fanout_ms", "judge_ms"):
+            line[k] = line["consensus"].get(k)
     if rank == 0 and world == 1 and not args.no_cpu:
         line["cpu_baseline"], _ = cpu_sample()
     if rank == 0:
         print(json.dumps(line), flush=True)
-    eng.close()
-    if dist is not None:
-        dist.destroy_process_group()
+    barrier()
+    ranks.close()
 
 
 def main():
@@ -241,6 +352,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--no-extra", action="store_true", help="skip the 8B decode and consensus (config 3) legs")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))

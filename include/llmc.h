@@ -73,7 +73,7 @@ typedef struct llmc_config {
 #define LLMC_FLAG_KV_BF16 4  /* store the KV cache in bf16 (default fp32; see DESIGN.md "precision") */
 #define LLMC_FLAG_PREFILL_BF16 8 /* prefill GEMM activations as one bf16 (default: a bf16 hi+lo pair) */
 #define LLMC_FLAG_NO_MEGAKERNEL 16 /* batch-1 decode as 81 kernels per step instead of one persistent kernel */
-#define LLMC_FLAG_RING_BARRIERS 64 /* ring kernel with grid barriers between phases (decode_ring.cu) instead of tagged-word hand-overs (decode_flow.cu) */
+#define LLMC_FLAG_RING_FLOW 64 /* experimental: ring kernel with tagged-word hand-overs (decode_flow.cu) instead of grid barriers between phases (decode_ring.cu) */
 #define LLMC_FLAG_NO_RING 32 /* persistent batch-1 decode pulls weights through registers (decode_mega.cu) instead of the TMA shared-memory ring (decode_ring.cu) */
 
 typedef struct llmc_stats {

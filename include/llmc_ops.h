@@ -97,7 +97,8 @@ int llmc_debug_kv(llmc_engine* e, int slot, int layer, int pos, void* k, void* v
  * looks the array's device address up and fills a small table in it; make that first call before any
  * stream capture begins.  All calls share the one array: it is cleared where the kernel needs zeros,
  * but two calls whose kernels can overlap on one GPU (different streams, different threads) race.
- * Neither cudaMalloc/cudaFree nor any allocating library routine is called. */
+ * Neither cudaMalloc/cudaFree nor any allocating library routine is called.  The caller's current
+ * device is left as it was (the call selects `device` internally and puts the previous one back). */
 #define LLMC_NOALLOC_MAX_BATCH 8
 #define LLMC_NOALLOC_MAX_VOCAB 262144
 int llmc_lmhead_argmax_noalloc(int device, int V, int K, int B, const uint16_t* d_W, const float* d_x,

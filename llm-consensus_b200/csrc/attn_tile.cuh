@@ -43,6 +43,9 @@ __device__ __forceinline__ void unpack_chunk(const uint4& w, float (&f)[16 / siz
 //   qs  [G][D] fp32 q of the GQA group (shared memory)         pw  [G][TP+1] per-warp exchange buffer (smem)
 //   kl / vl: the tile's first K / V row, already offset by this lane's first chunk (c * EPV)
 //   valid: positions of the tile that exist; m, l warp-uniform; o partial over this lane's rows
+//   kl / vl carry no __restrict__: a caller may have appended the newest row to the pools earlier in the same kernel
+//   (attn_decode.cu, decode_flow.cu), and const + __restrict__ would let the compiler read through the
+//   non-coherent path
 template <bool CG>
 __device__ __forceinline__ uint4 ld16(const void* p) {
   // CG: read through L2 only (the caller's kernel communicates this data between SMs)
@@ -54,7 +57,7 @@ __device__ __forceinline__ uint4 ld16(const void* p) {
 // requested at once: one memory round trip per phase instead of two)
 template <int D, int G, typename KVT, bool CG = false, int LDF = LaneMap<D, G, KVT>::LD>
 __device__ __forceinline__ void attn_tile_step(const float* __restrict__ qs, float* __restrict__ pw,
-                                               const KVT* __restrict__ kl, const KVT* __restrict__ vl, int valid,
+                                               const KVT* kl, const KVT* vl, int valid,
                                                float scale, float (&m)[G], float (&l)[G],
                                                float (&o)[G][LaneMap<D, G, KVT>::EPL]) {
   using M = LaneMap<D, G, KVT>;
@@ -148,6 +151,119 @@ __device__ __forceinline__ void attn_tile_step(const float* __restrict__ qs, flo
       }
     }
     __syncwarp();                                      // p values consumed before the next tile's scores
+}
+
+// ---- the same tile step split in two, for callers that can fetch a tile long before they may use it (the one-kernel
+// decode step fetches each warp's first K/V tile while it waits for the grid barrier that publishes q): the whole tile
+// (K and V) sits in registers, NP * CPL 16-byte chunks each.
+template <int D, int G, typename KVT>
+struct TileRegs {
+  using M = LaneMap<D, G, KVT>;
+  uint4 k[M::NP][M::CPL];
+  uint4 v[M::NP][M::CPL];
+};
+
+// rows: positions of the tile that may be read now (rows at or past it alias row rows - 1, as in attn_tile_step)
+template <int D, int G, typename KVT, bool CG>
+__device__ __forceinline__ void attn_tile_fetch(const KVT* kl, const KVT* vl, int rows, TileRegs<D, G, KVT>& t) {
+  using M = LaneMap<D, G, KVT>;
+  const int sub = (threadIdx.x & 31) / M::LPR;
+#pragma unroll
+  for (int pp = 0; pp < M::NP; ++pp) {
+    const int row = min(pp * M::RPP + sub, rows - 1);
+#pragma unroll
+    for (int j = 0; j < M::CPL; ++j) {
+      t.k[pp][j] = ld16<CG>(kl + (size_t)row * D + j * M::LPR * M::EPV);
+      t.v[pp][j] = ld16<CG>(vl + (size_t)row * D + j * M::LPR * M::EPV);
+    }
+  }
+}
+// (re)loads one row of a fetched tile: the lanes that hold row `r` read it again
+template <int D, int G, typename KVT, bool CG>
+__device__ __forceinline__ void attn_tile_fetch_row(const KVT* kl, const KVT* vl, int r, TileRegs<D, G, KVT>& t) {
+  using M = LaneMap<D, G, KVT>;
+  const int sub = (threadIdx.x & 31) / M::LPR;
+#pragma unroll
+  for (int pp = 0; pp < M::NP; ++pp) {
+    if (pp * M::RPP + sub == r) {
+#pragma unroll
+      for (int j = 0; j < M::CPL; ++j) {
+        t.k[pp][j] = ld16<CG>(kl + (size_t)r * D + j * M::LPR * M::EPV);
+        t.v[pp][j] = ld16<CG>(vl + (size_t)r * D + j * M::LPR * M::EPV);
+      }
+    }
+  }
+}
+// folds a fetched tile into the running softmax state: the arithmetic of attn_tile_step, operation for operation
+template <int D, int G, typename KVT>
+__device__ __forceinline__ void attn_tile_fold(const float* __restrict__ qs, float* __restrict__ pw,
+                                               const TileRegs<D, G, KVT>& t, int valid, float scale, float (&m)[G],
+                                               float (&l)[G], float (&o)[G][LaneMap<D, G, KVT>::EPL]) {
+  using M = LaneMap<D, G, KVT>;
+  constexpr int EPV = M::EPV, LPR = M::LPR, CPL = M::CPL, RPP = M::RPP, NP = M::NP, EPL = M::EPL;
+  const int lane = threadIdx.x & 31;
+  const int sub = lane / LPR, c = lane % LPR;
+#pragma unroll
+  for (int pp = 0; pp < NP; ++pp) {
+    float sc[G];
+#pragma unroll
+    for (int h = 0; h < G; ++h) sc[h] = 0.f;
+#pragma unroll
+    for (int j = 0; j < CPL; ++j) {
+      float kf[EPV];
+      unpack_chunk<KVT>(t.k[pp][j], kf);
+#pragma unroll
+      for (int h = 0; h < G; ++h) {
+        const float* qh = qs + h * D + (c + j * LPR) * EPV;
+#pragma unroll
+        for (int e = 0; e < EPV; e += 4) {
+          const float4 qv = *reinterpret_cast<const float4*>(qh + e);
+          sc[h] = fmaf(kf[e], qv.x, sc[h]);
+          sc[h] = fmaf(kf[e + 1], qv.y, sc[h]);
+          sc[h] = fmaf(kf[e + 2], qv.z, sc[h]);
+          sc[h] = fmaf(kf[e + 3], qv.w, sc[h]);
+        }
+      }
+    }
+#pragma unroll
+    for (int h = 0; h < G; ++h) {
+#pragma unroll
+      for (int off = LPR / 2; off > 0; off >>= 1) sc[h] += __shfl_xor_sync(0xffffffffu, sc[h], off);
+      if (c == 0) pw[h * (TP + 1) + pp * RPP + sub] = sc[h] * scale;
+    }
+  }
+  __syncwarp();
+#pragma unroll
+  for (int h = 0; h < G; ++h) {
+    const float sh = (lane < valid) ? pw[h * (TP + 1) + lane] : -INFINITY;
+    const float mn = fmaxf(m[h], warp_max(sh));
+    const float corr = __expf(m[h] - mn);
+    const float ph = (lane < valid) ? __expf(sh - mn) : 0.f;
+    l[h] = l[h] * corr + warp_sum(ph);
+    m[h] = mn;
+    pw[h * (TP + 1) + lane] = ph;
+#pragma unroll
+    for (int e = 0; e < EPL; ++e) o[h][e] *= corr;
+  }
+  __syncwarp();
+#pragma unroll
+  for (int pp = 0; pp < NP; ++pp) {
+    const int row = pp * RPP + sub;
+    const bool live = row < valid;
+    float pr[G];
+#pragma unroll
+    for (int h = 0; h < G; ++h) pr[h] = live ? pw[h * (TP + 1) + row] : 0.f;
+#pragma unroll
+    for (int j = 0; j < CPL; ++j) {
+      float vf[EPV];
+      unpack_chunk<KVT>(t.v[pp][j], vf);
+#pragma unroll
+      for (int h = 0; h < G; ++h)
+#pragma unroll
+        for (int e = 0; e < EPV; ++e) o[h][j * EPV + e] = fmaf(pr[h], vf[e], o[h][j * EPV + e]);
+    }
+  }
+  __syncwarp();
 }
 
 // Sums the per-lane partial outputs over the row groups of the lane map and writes the warp's state

@@ -411,9 +411,10 @@ static int create_impl(llmc_engine* e, const llmc_config& c) {
                 decode_ring_supported(e->d.hidden, e->d.qd(), e->d.kd(), e->d.inter, e->d.vocab, e->d.q_heads, e->d.kv_heads,
                                       e->d.head_dim);
   {
-    // LLMC_FLAG_RING_BARRIERS (or LLMC_RING_FLOW=0) keeps the grid-barrier version of the ring kernel
+    // LLMC_FLAG_RING_FLOW (or LLMC_RING_FLOW=1) selects the barrier-free variant of the ring kernel (measured slower so
+    // far; kept as a comparator)
     const char* fl = getenv("LLMC_RING_FLOW");
-    const bool want_flow = fl ? atoi(fl) != 0 : !(c.flags & LLMC_FLAG_RING_BARRIERS);
+    const bool want_flow = fl ? atoi(fl) != 0 : (c.flags & LLMC_FLAG_RING_FLOW) != 0;
     e->use_flow = e->use_ring && want_flow &&
                   decode_flow_supported(e->d.hidden, e->d.qd(), e->d.kd(), e->d.inter, e->d.vocab, e->d.q_heads,
                                         e->d.kv_heads, e->d.head_dim, e->prop.multiProcessorCount);
@@ -501,10 +502,13 @@ static int create_impl(llmc_engine* e, const llmc_config& c) {
     if (int rc = dalloc(e, &e->mega_scratch, (size_t)d.q_heads * e->mega_max_tiles * (D + 2))) return rc;
     if (int rc = dalloc(e, &e->mega_part_val, (size_t)e->prop.multiProcessorCount)) return rc;
     if (int rc = dalloc(e, &e->mega_part_idx, (size_t)e->prop.multiProcessorCount)) return rc;
-    if (int rc = dalloc(e, &e->mega_barrier, 1)) return rc;
+    if (int rc = dalloc(e, &e->mega_barrier, 4)) return rc;   // [0] grid barrier / pacing counter, [1] attention-output counter
     if (int rc = dalloc(e, &e->mega_counters, (size_t)d.kv_heads)) return rc;
-    if (getenv("LLMC_MEGA_TRACE"))
-      if (int rc = dalloc(e, &e->mega_trace, (size_t)2 * (5 * d.layers + 1) * 64 + 16 + 5 * 256)) return rc;
+    if (getenv("LLMC_MEGA_TRACE")) {
+      const size_t nt = (size_t)2 * (5 * d.layers + 1) * 64 + 16 + 5 * 256;
+      if (int rc = dalloc(e, &e->mega_trace, nt)) return rc;
+      E_TRY(cudaMemsetAsync(e->mega_trace, 0, nt * sizeof(unsigned long long), e->stream));
+    }
     E_TRY(cudaMemsetAsync(e->mega_counters, 0, (size_t)d.kv_heads * sizeof(unsigned), e->stream));
     if (e->use_flow) {
       e->flow_nwords = decode_flow_words(H, QD, KD, I, d.q_heads, d.kv_heads, D, e->prop.multiProcessorCount);
@@ -531,6 +535,10 @@ static int create_impl(llmc_engine* e, const llmc_config& c) {
   E_TRY(cudaStreamSynchronize(e->stream));
   E_TRY(cudaGetLastError());
   stage("workspaces, sync");
+  if (init_trace)
+    fprintf(stderr, "[init dev %d] batch-1 decode path: %s\n", c.device,
+            !e->use_mega ? "kernel graph" : e->use_flow ? "decode_flow (ring, tagged-word hand-overs)"
+                                          : e->use_ring ? "decode_ring (ring, grid barriers)" : "decode_mega (register streaming)");
   e->stats.graph_enabled = e->use_graph;
   e->stats.pdl_enabled = e->use_pdl;
   return LLMC_OK;
@@ -735,7 +743,7 @@ static int decode_group(llmc_engine* e, const int32_t* slots, int32_t nslots, in
       m.ring_poll_mode = pm ? atoi(pm) : 1;
     }
     m.trace = (e->mega_trace && nsteps <= 64) ? e->mega_trace : nullptr;
-    E_TRY(cudaMemsetAsync(e->mega_barrier, 0, sizeof(unsigned), s));
+    E_TRY(cudaMemsetAsync(e->mega_barrier, 0, 4 * sizeof(unsigned), s));
     if (e->use_flow) {
       // hand-over tags continue from launch to launch, so a word left by an earlier call never matches
       const unsigned need = (unsigned)nsteps * (unsigned)(5 * d.layers + 1);
@@ -786,8 +794,13 @@ static int decode_group(llmc_engine* e, const int32_t* slots, int32_t nslots, in
       cnt[k]++;
     }
     for (int k = 0; k < 6; ++k)
-      if (cnt[k]) fprintf(stderr, "[mega trace] %-7s phase %.2f us (block 0 waited %.2f us at its barrier) x%d\n", names[k],
+      if (cnt[k]) fprintf(stderr, "[%s trace] %-7s phase %.2f us (block 0 waited %.2f us at its barrier) x%d\n", e->use_flow ? "flow" : e->use_ring ? "ring" : "mega", names[k],
                           phase[k] / cnt[k] / 1e3, wait[k] / cnt[k] / 1e3, cnt[k]);
+    if (e->use_flow) {
+      const unsigned long long* st = t.data() + (size_t)2 * nb;
+      fprintf(stderr, "[flow stats] block 0 warp 0, cycles: total %llu = wait-full %llu + activation loads %llu + slots %llu "
+                      "(%llu slots seen) + hand-overs (all-writer) %llu + rest\n", st[4], st[0], st[1], st[2], st[5], st[3]);
+    }
     if (e->use_ring && !e->use_flow) {
       const unsigned long long* st = t.data() + (size_t)2 * nb;
       if (nsteps > 1) {

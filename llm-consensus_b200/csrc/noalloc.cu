@@ -26,7 +26,10 @@ namespace {
 
 constexpr int NA_MAX_BATCH = LLMC_NOALLOC_MAX_BATCH;
 constexpr int NA_MAX_VOCAB = LLMC_NOALLOC_MAX_VOCAB;
-constexpr int NA_MAX_BLOCKS = (NA_MAX_VOCAB / 4 + 1) / 2;  // gemv_lmhead_blocks(NA_MAX_VOCAB)
+// candidates per batch row the array has room for; every call checks the block count the kernels would
+// actually use (gemv_lmhead_blocks / gemv_mma_lmhead_blocks) against it, so a change of their launch
+// geometry is refused loudly instead of overrunning the array
+constexpr int NA_MAX_BLOCKS = (NA_MAX_VOCAB / 4 + 1) / 2;
 // layout (bytes): [0,256) control words cleared before every launch: block counter, step counter,
 // pending-token and length cells the kernel's finalisation writes; [256,512) identity slot table,
 // written once at set-up; then the per-block argmax candidates (values, then indices)
@@ -67,7 +70,19 @@ int llmc_lmhead_argmax_noalloc(int device, int V, int K, int B, const uint16_t* 
                                      ", the size the built-in scratch was compiled for");
   if (K < 256 || K % 256) return nfail(LLMC_ERR_INVALID, "llmc_lmhead_argmax_noalloc: K must be a positive multiple of 256");
   if (device < 0 || device >= MAX_DEVICES) return nfail(LLMC_ERR_INVALID, "llmc_lmhead_argmax_noalloc: bad device ordinal");
-  cudaError_t ce = cudaSetDevice(device);
+  const int need_blocks = B == 1 ? gemv_lmhead_blocks(V) : gemv_mma_lmhead_blocks(V);
+  if (need_blocks > NA_MAX_BLOCKS)
+    return nfail(LLMC_ERR_LIMIT, "llmc_lmhead_argmax_noalloc: the kernel would use " + std::to_string(need_blocks) +
+                                     " blocks, the built-in scratch holds candidates of " + std::to_string(NA_MAX_BLOCKS));
+  // the caller's current device is put back before every return
+  int prev_device = -1;
+  cudaError_t ce = cudaGetDevice(&prev_device);
+  if (ce != cudaSuccess) return nfail(LLMC_ERR_CUDA, std::string("cudaGetDevice: ") + cudaGetErrorString(ce));
+  struct Restore {
+    int dev;
+    ~Restore() { if (dev >= 0) cudaSetDevice(dev); }
+  } restore{prev_device == device ? -1 : prev_device};
+  ce = cudaSetDevice(device);
   if (ce != cudaSuccess) return nfail(LLMC_ERR_CUDA, std::string("cudaSetDevice: ") + cudaGetErrorString(ce));
   cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
 
@@ -82,7 +97,8 @@ int llmc_lmhead_argmax_noalloc(int device, int V, int K, int B, const uint16_t* 
         return nfail(LLMC_ERR_CUDA, std::string("cudaGetSymbolAddress(scratch): ") + cudaGetErrorString(ce));
       int ident[NA_MAX_BATCH];
       for (int i = 0; i < NA_MAX_BATCH; ++i) ident[i] = i;
-      ce = cudaMemcpy(p + NA_SLOTS_OFF, ident, sizeof(ident), cudaMemcpyHostToDevice);
+      // on the caller's stream, ahead of the launch below (a pageable source is staged before the call returns)
+      ce = cudaMemcpyAsync(p + NA_SLOTS_OFF, ident, sizeof(ident), cudaMemcpyHostToDevice, s);
       if (ce != cudaSuccess) return nfail(LLMC_ERR_CUDA, std::string("scratch set-up copy: ") + cudaGetErrorString(ce));
       g_ptr[device] = p;
     }

@@ -12,29 +12,48 @@ import (
 	"context"
 	"fmt"
 	"runtime"
+	"sync"
 	"time"
 	"unsafe"
 )
 
 type LocalConfig struct {
-	Shape        int    // C.LLMC_SHAPE_LLAMA_1B / _8B
-	Seed         uint64 // --seed (+ the -sN suffix of the model name)
-	Device       int    // --device; the runner maps model i to GPU i
-	WeightsPath  string // --weights: .safetensors file or shard directory, HF Llama names ("" = seeded random init)
+	Shape        int     // C.LLMC_SHAPE_LLAMA_1B / _8B
+	Seed         uint64  // --seed (+ the -sN suffix of the model name)
+	Device       int     // --device; the runner maps model i to GPU i
+	WeightsPath  string  // --weights: .safetensors file or shard directory, HF Llama names ("" = seeded random init)
 	MaxNewTokens int
 	MaxCtx       int
+	MaxSlots     int     // queries in flight on this instance (its entries in --models, +1 if it is the judge); 0 -> 4
+	StopIDs      []int32 // generation ends before the first of these ids (128001 / 128009 for Llama-3)
+}
+
+// job is one QueryStream call in the hands of the scheduler goroutine.
+type job struct {
+	slot C.int32_t
+	left int           // tokens still to decode
+	out  chan []int32  // decoded chunks; closed when left reaches 0 or on error (err set before the close)
+	err  error
+	quit chan struct{} // closed by the caller when it gives up (ctx done, stop id)
+	gone chan struct{} // closed by the scheduler once the job is in no running llmc_decode call
 }
 
 type Local struct {
 	e     *C.llmc_engine
 	cfg   LocalConfig
 	vocab int
+	slots chan struct{} // counting semaphore over the engine's sequence slots
+	join  chan *job
+	once  sync.Once
 }
 
 func NewLocal(cfg LocalConfig) (*Local, error) {
+	if cfg.MaxSlots <= 0 {
+		cfg.MaxSlots = 4
+	}
 	var c C.llmc_config
 	c.device, c.shape, c.seed = C.int32_t(cfg.Device), C.int32_t(cfg.Shape), C.uint64_t(cfg.Seed)
-	c.max_slots, c.max_ctx = 2, C.int32_t(cfg.MaxCtx)
+	c.max_slots, c.max_ctx = C.int32_t(cfg.MaxSlots), C.int32_t(cfg.MaxCtx)
 	if cfg.WeightsPath != "" {
 		p := C.CString(cfg.WeightsPath)
 		defer C.free(unsafe.Pointer(p))
@@ -44,13 +63,21 @@ func NewLocal(cfg LocalConfig) (*Local, error) {
 	if rc := C.llmc_engine_create(&c, &e); rc != C.LLMC_OK {
 		return nil, fmt.Errorf("local provider: %s", C.GoString(C.llmc_last_error(nil)))
 	}
-	return &Local{e: e, cfg: cfg, vocab: 128256}, nil
+	l := &Local{e: e, cfg: cfg, vocab: 128256, slots: make(chan struct{}, cfg.MaxSlots), join: make(chan *job, cfg.MaxSlots)}
+	for i := 0; i < cfg.MaxSlots; i++ {
+		l.slots <- struct{}{}
+	}
+	return l, nil
 }
 
 func (l *Local) Query(ctx context.Context, req Request) (Response, error) {
 	return l.QueryStream(ctx, req, nil) // never called by the CLI path (runner.go:92, judge.go:96)
 }
 
+// QueryStream prefills its own sequence slot, then hands the decode loop to the scheduler goroutine, which
+// advances every live sequence of this instance together: one llmc_decode(slots[], n, k) per chunk, i.e. one pass
+// over the weights per step however many --models entries name this model (runner.go:62 starts one goroutine per
+// entry, duplicates included).  Chunks come back over a channel and are emitted here, on the caller's goroutine.
 func (l *Local) QueryStream(ctx context.Context, req Request, cb StreamCallback) (Response, error) {
 	start := time.Now()
 	// Every llmc_* call selects its device itself, so goroutine migration is harmless; locking the
@@ -62,6 +89,15 @@ func (l *Local) QueryStream(ctx context.Context, req Request, cb StreamCallback)
 	if len(ids) == 0 {
 		ids = []int32{'\n'}
 	}
+	if l.cfg.MaxNewTokens <= 0 {
+		return Response{Model: req.Model, Provider: "local", Latency: time.Since(start)}, nil
+	}
+	select { // a sequence slot: wait for one rather than fail when callers outnumber slots
+	case <-l.slots:
+	case <-ctx.Done():
+		return Response{}, ctx.Err()
+	}
+	defer func() { l.slots <- struct{}{} }()
 	var slot C.int32_t
 	if C.llmc_seq_alloc(l.e, &slot) != C.LLMC_OK {
 		return Response{}, l.err("allocating a sequence slot")
@@ -72,8 +108,21 @@ func (l *Local) QueryStream(ctx context.Context, req Request, cb StreamCallback)
 	if C.llmc_prefill(l.e, slot, (*C.int32_t)(unsafe.Pointer(&ids[0])), C.int32_t(len(ids)), &first, nil) != C.LLMC_OK {
 		return Response{}, l.err("prefill")
 	}
-	content := ""
+	content, stopped := "", false
 	emit := func(t []int32) {
+		for i, id := range t {
+			for _, s := range l.cfg.StopIDs {
+				if id == s && !stopped {
+					stopped, t = true, t[:i] // end-of-text: the chunk is cut before it
+				}
+			}
+			if stopped {
+				break
+			}
+		}
+		if len(t) == 0 {
+			return
+		}
 		chunk := Detokenize(t)
 		content += chunk
 		if cb != nil {
@@ -81,27 +130,107 @@ func (l *Local) QueryStream(ctx context.Context, req Request, cb StreamCallback)
 		}
 	}
 	emit([]int32{int32(first)})
-	const chunk = 16
-	toks := make([]int32, chunk)
-	for left := l.cfg.MaxNewTokens - 1; left > 0; {
-		if err := ctx.Err(); err != nil { // per-model timeout (runner.go:65) and SIGINT (main.go:90)
-			return Response{}, err // lands in warnings as "<model>: context deadline exceeded" (runner.go:101)
+	if left := l.cfg.MaxNewTokens - 1; left > 0 && !stopped {
+		const chunk = 16
+		j := &job{slot: slot, left: left, out: make(chan []int32, left/chunk+2), quit: make(chan struct{}), gone: make(chan struct{})}
+		l.once.Do(func() { go l.schedule(chunk) })
+		l.join <- j
+		leave := func() { // the deferred llmc_seq_free must not run while a decode call still holds the slot
+			close(j.quit)
+			<-j.gone
 		}
-		k := min(left, chunk)
-		if C.llmc_decode(l.e, &slot, 1, C.int32_t(k), (*C.int32_t)(unsafe.Pointer(&toks[0])), nil) != C.LLMC_OK {
-			return Response{}, l.err("decode")
+	loop:
+		for !stopped {
+			select {
+			case t, ok := <-j.out:
+				if !ok {
+					break loop
+				}
+				emit(t)
+			case <-ctx.Done(): // per-model timeout (runner.go:65) and SIGINT (main.go:90)
+				leave()
+				return Response{}, ctx.Err() // lands in warnings as "<model>: context deadline exceeded" (runner.go:101)
+			}
 		}
-		emit(toks[:k])
-		left -= k
+		leave()
+		if j.err != nil {
+			return Response{}, j.err
+		}
 	}
 	return Response{Model: req.Model, Content: content, Provider: "local", Latency: time.Since(start)}, nil
+}
+
+// schedule runs on its own goroutine for the life of the provider.
+func (l *Local) schedule(chunk int) {
+	runtime.LockOSThread()
+	var live []*job
+	for {
+		if len(live) == 0 {
+			j, ok := <-l.join
+			if !ok {
+				return
+			}
+			live = append(live, j)
+		}
+		for more := true; more; { // whoever else has finished its prefill joins at this chunk boundary
+			select {
+			case j := <-l.join:
+				live = append(live, j)
+			default:
+				more = false
+			}
+		}
+		keep := live[:0]
+		for _, j := range live { // callers that gave up leave here, between two decode calls
+			select {
+			case <-j.quit:
+				close(j.gone)
+			default:
+				keep = append(keep, j)
+			}
+		}
+		live = keep
+		if len(live) == 0 {
+			continue
+		}
+		k := chunk
+		slots := make([]C.int32_t, len(live))
+		for i, j := range live {
+			k, slots[i] = min(k, j.left), j.slot
+		}
+		toks := make([]int32, len(live)*k)
+		rc := C.llmc_decode(l.e, &slots[0], C.int32_t(len(live)), C.int32_t(k), (*C.int32_t)(unsafe.Pointer(&toks[0])), nil)
+		keep = live[:0]
+		for i, j := range live {
+			if rc != C.LLMC_OK {
+				j.err = l.err("decode")
+				j.left = 0
+			} else {
+				j.out <- toks[i*k : (i+1)*k : (i+1)*k]
+				j.left -= k
+			}
+			if j.left > 0 {
+				keep = append(keep, j)
+				continue
+			}
+			close(j.out)
+			go func(j *job) { // finished: acknowledge its leave() whenever it comes
+				<-j.quit
+				close(j.gone)
+			}(j)
+		}
+		live = keep
+	}
 }
 
 func (l *Local) err(what string) error {
 	return fmt.Errorf("local provider: %s: %s", what, C.GoString(C.llmc_last_error(l.e)))
 }
 
-func (l *Local) Close() { C.llmc_engine_destroy(l.e) }
+func (l *Local) Close() {
+	close(l.join)
+	C.llmc_engine_destroy(l.e)
+}
 
 // LocalDeviceCount is what createProvider uses to deal models to GPUs round-robin.
 func LocalDeviceCount() int { return int(C.llmc_device_count()) }

@@ -174,6 +174,8 @@ struct LocalConfig {
   int max_ctx = 8192;
   int chunk = 16;            // decode steps per C call; ctx is polled between chunks
   int flags = 0;
+  int max_slots = 4;         // sequences that can be in flight on this instance; further callers wait for a slot
+  std::vector<int32_t> stop_ids;  // generation ends before the first of these ids (e.g. 128001 / 128009 for Llama-3)
 };
 // provider.NewLocal: builds an engine through the C ABI (include/llmc.h); Provider tag "local"
 Error NewLocal(const LocalConfig& cfg, std::shared_ptr<Provider>* out);

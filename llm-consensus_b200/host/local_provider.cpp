@@ -3,7 +3,12 @@
 // (/root/reference/internal/provider/openai.go:141-210): build the request, run it, call the
 // callback synchronously on the caller's thread for every chunk, return
 // Response{Model: req.Model, Content, Provider, Latency}.
+#include <algorithm>
 #include <chrono>
+#include <condition_variable>
+#include <deque>
+#include <mutex>
+#include <thread>
 
 #include "../../include/llmc.h"
 #include "host.hpp"
@@ -12,10 +17,25 @@ namespace host {
 
 namespace {
 
+// One model instance.  The reference runner starts one goroutine per entry of --models against the shared
+// provider (runner.go:62-95, no dedupe), so several QueryStream calls can be in flight on one instance.  They do
+// not take turns: every caller prefills its own sequence slot, then hands the decode loop to a scheduler thread
+// that advances ALL live sequences together, one llmc_decode(slots[], n, k) per chunk -- one pass over the
+// weights per step for the whole group (the wide decode path) instead of one pass per caller.  Chunks go back
+// to the callers, which emit them through their own callback on their own thread, as provider.go:10 requires.
 class Local : public Provider {
  public:
-  Local(llmc_engine* e, const LocalConfig& cfg, int vocab) : e_(e), cfg_(cfg), vocab_(vocab) {}
-  ~Local() override { llmc_engine_destroy(e_); }
+  Local(llmc_engine* e, const LocalConfig& cfg, int vocab, int max_slots)
+      : e_(e), cfg_(cfg), vocab_(vocab), free_slots_(max_slots) {}
+  ~Local() override {
+    {
+      std::lock_guard<std::mutex> lk(mu_);
+      stop_ = true;
+    }
+    sched_cv_.notify_all();
+    if (sched_.joinable()) sched_.join();
+    llmc_engine_destroy(e_);
+  }
 
   Error Query(const Context& ctx, const Request& req, Response* out) override {
     return QueryStream(ctx, req, nullptr, out);  // never called by the CLI path (runner.go:92, judge.go:96)
@@ -30,44 +50,164 @@ class Local : public Provider {
                         std::to_string(cfg_.max_new_tokens) + " new tokens exceeds the context of " +
                         std::to_string(cfg_.max_ctx));
     if (!ctx.Err().empty()) return Error::New(ctx.Err());
-    int32_t slot = -1;
-    if (llmc_seq_alloc(e_, &slot) != LLMC_OK) return fail("allocating a sequence slot");
-    struct Free {
-      llmc_engine* e;
-      int32_t s;
-      ~Free() { llmc_seq_free(e, s); }
-    } guard{e_, slot};
+    out->Model = req.Model;
+    out->Provider = "local";
+    out->Content.clear();
+    if (cfg_.max_new_tokens <= 0) {   // nothing asked for: an empty answer, like a remote stream with no delta
+      out->Latency = since(start);
+      return Error::Nil();
+    }
+    // a sequence slot: wait for one instead of failing when more callers arrive than the engine has slots
+    {
+      std::unique_lock<std::mutex> lk(mu_);
+      while (free_slots_ == 0) {
+        slot_cv_.wait_for(lk, std::chrono::milliseconds(5));
+        if (!ctx.Err().empty()) return Error::New(ctx.Err());
+      }
+      --free_slots_;
+    }
+    Job job;
+    struct Release {
+      Local* p;
+      Job* j;
+      ~Release() { p->release(j); }
+    } guard{this, &job};
+    if (llmc_seq_alloc(e_, &job.slot) != LLMC_OK) return fail("allocating a sequence slot");
     std::string content;
+    bool stopped = false;
     auto emit = [&](const int32_t* t, size_t n) {
+      for (size_t i = 0; i < n && !stopped; ++i)
+        if (std::find(cfg_.stop_ids.begin(), cfg_.stop_ids.end(), t[i]) != cfg_.stop_ids.end()) {
+          stopped = true;   // end-of-text: the chunk is cut before it
+          n = i;
+        }
+      if (n == 0) return;
       const std::string chunk = Detokenize(t, n);
       content += chunk;
       if (cb) cb(chunk);
     };
     int32_t first = -1;
-    if (llmc_prefill(e_, slot, ids.data(), (int32_t)ids.size(), &first, nullptr) != LLMC_OK) return fail("prefill");
+    if (llmc_prefill(e_, job.slot, ids.data(), (int32_t)ids.size(), &first, nullptr) != LLMC_OK) return fail("prefill");
     emit(&first, 1);
-    std::vector<int32_t> toks(cfg_.chunk);
-    for (int left = cfg_.max_new_tokens - 1; left > 0;) {
-      // the reference's backends honour ctx through the HTTP request (openai.go:155); here it is polled
-      // between decode chunks, so a cancel / deadline costs at most one chunk
-      if (!ctx.Err().empty()) return Error::New(ctx.Err());
-      const int k = left < cfg_.chunk ? left : cfg_.chunk;
-      if (llmc_decode(e_, &slot, 1, k, toks.data(), nullptr) != LLMC_OK) return fail("decode");
-      emit(toks.data(), (size_t)k);
-      left -= k;
+    job.left = cfg_.max_new_tokens - 1;
+    if (job.left > 0 && !stopped) {
+      {
+        std::lock_guard<std::mutex> lk(mu_);
+        jobs_.push_back(&job);
+        if (!sched_.joinable()) sched_ = std::thread([this] { schedule(); });
+      }
+      sched_cv_.notify_all();
+      int got = 0;
+      const int want = job.left;
+      std::vector<int32_t> chunk;
+      while (got < want && !stopped) {
+        {
+          std::unique_lock<std::mutex> lk(mu_);
+          // the reference's backends honour ctx through the HTTP request (openai.go:155); here it is polled while
+          // waiting for the next chunk, so a cancel / deadline costs at most one chunk
+          while (job.ready.empty() && job.err.empty()) {
+            job.cv.wait_for(lk, std::chrono::milliseconds(5));
+            if (!ctx.Err().empty()) return Error::New(ctx.Err());
+          }
+          if (!job.err.empty()) return Error::New("local provider: decode: " + job.err);
+          chunk.assign(job.ready.begin(), job.ready.end());
+          job.ready.clear();
+        }
+        if (!ctx.Err().empty()) return Error::New(ctx.Err());
+        emit(chunk.data(), chunk.size());
+        got += (int)chunk.size();
+      }
     }
-    out->Model = req.Model;
     out->Content = content;
-    out->Provider = "local";
-    out->Latency = std::chrono::duration_cast<std::chrono::nanoseconds>(std::chrono::steady_clock::now() - start).count();
+    out->Latency = since(start);
     return Error::Nil();
   }
 
  private:
+  struct Job {
+    int32_t slot = -1;
+    int left = 0;                  // tokens still to decode (scheduler's view)
+    bool in_flight = false;        // part of the llmc_decode call that is running now
+    std::deque<int32_t> ready;     // decoded, not yet picked up by the caller
+    std::string err;
+    std::condition_variable cv;
+  };
+
+  static int64_t since(std::chrono::steady_clock::time_point t0) {
+    return std::chrono::duration_cast<std::chrono::nanoseconds>(std::chrono::steady_clock::now() - t0).count();
+  }
+
+  // caller side, on every exit path: leave the scheduler's list (after the decode call that may still hold the
+  // slot), free the sequence slot, hand the slot count back
+  void release(Job* j) {
+    {
+      std::unique_lock<std::mutex> lk(mu_);
+      j->left = 0;
+      while (j->in_flight) j->cv.wait_for(lk, std::chrono::milliseconds(1));
+      jobs_.erase(std::remove(jobs_.begin(), jobs_.end(), j), jobs_.end());
+    }
+    if (j->slot >= 0) llmc_seq_free(e_, j->slot);
+    {
+      std::lock_guard<std::mutex> lk(mu_);
+      ++free_slots_;
+    }
+    slot_cv_.notify_one();
+  }
+
+  // scheduler thread: one llmc_decode per chunk over every sequence that still wants tokens
+  void schedule() {
+    std::vector<Job*> batch;
+    std::vector<int32_t> slots, toks;
+    std::unique_lock<std::mutex> lk(mu_);
+    while (true) {
+      sched_cv_.wait(lk, [&] {
+        if (stop_) return true;
+        for (Job* j : jobs_)
+          if (j->left > 0) return true;
+        return false;
+      });
+      if (stop_) return;
+      batch.clear();
+      slots.clear();
+      int k = cfg_.chunk;
+      for (Job* j : jobs_)
+        if (j->left > 0 && (int)batch.size() < 128) {
+          batch.push_back(j);
+          slots.push_back(j->slot);
+          k = std::min(k, j->left);
+          j->in_flight = true;
+        }
+      const int n = (int)batch.size();
+      toks.resize((size_t)n * k);
+      lk.unlock();
+      const int rc = llmc_decode(e_, slots.data(), n, k, toks.data(), nullptr);
+      const std::string err = rc == LLMC_OK ? "" : llmc_last_error(e_);
+      lk.lock();
+      for (int i = 0; i < n; ++i) {
+        Job* j = batch[i];
+        j->in_flight = false;
+        if (rc != LLMC_OK) {
+          j->err = err.empty() ? "llmc_decode failed" : err;
+          j->left = 0;
+        } else if (j->left > 0) {   // (0: the caller gave up while the call ran)
+          j->ready.insert(j->ready.end(), toks.begin() + (size_t)i * k, toks.begin() + (size_t)(i + 1) * k);
+          j->left -= k;
+        }
+        j->cv.notify_all();
+      }
+    }
+  }
+
   Error fail(const std::string& what) { return Error::New("local provider: " + what + ": " + llmc_last_error(e_)); }
   llmc_engine* e_;
   LocalConfig cfg_;
   int vocab_;
+  std::mutex mu_;
+  std::condition_variable sched_cv_, slot_cv_;
+  std::vector<Job*> jobs_;
+  int free_slots_;
+  bool stop_ = false;
+  std::thread sched_;
 };
 
 }  // namespace
@@ -80,13 +220,14 @@ Error NewLocal(const LocalConfig& cfg, std::shared_ptr<Provider>* out) {
   c.head_dim = cfg.head_dim; c.inter = cfg.inter; c.vocab = cfg.vocab; c.tied = cfg.tied;
   c.seed = cfg.seed;
   c.weights_path = cfg.weights_path.empty() ? nullptr : cfg.weights_path.c_str();
-  c.max_slots = 2;
+  const int max_slots = std::max(1, std::min(cfg.max_slots, 128));
+  c.max_slots = max_slots;
   c.max_ctx = cfg.max_ctx;
   c.flags = cfg.flags;
   llmc_engine* e = nullptr;
   if (llmc_engine_create(&c, &e) != LLMC_OK) return Error::New(std::string("local provider: ") + llmc_last_error(nullptr));
   const int vocab = cfg.shape == LLMC_SHAPE_CUSTOM ? cfg.vocab : 128256;
-  *out = std::make_shared<Local>(e, cfg, vocab);
+  *out = std::make_shared<Local>(e, cfg, vocab, max_slots);
   return Error::Nil();
 }
 

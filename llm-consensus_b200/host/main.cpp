@@ -162,7 +162,10 @@ bool splitSeedSuffix(const std::string& model, std::string* base, uint64_t* off)
   return true;
 }
 
-Error createProvider(const std::string& model, const Config& cfg, int* next_device, std::shared_ptr<Provider>* out) {
+// uses: how many QueryStream calls can be in flight on this model at once (its entries in --models, duplicates
+// included as runner.go:62 starts one goroutine per entry, plus one if it is also the judge)
+Error createProvider(const std::string& model, const Config& cfg, int* next_device, int uses,
+                     std::shared_ptr<Provider>* out) {
   for (const std::string& s : cfg.stubs) {  // NAME=PROVIDER:DELAY_MS:CONTENT
     const size_t eq = s.find('=');
     if (eq == std::string::npos || s.substr(0, eq) != model) continue;
@@ -215,6 +218,7 @@ Error createProvider(const std::string& model, const Config& cfg, int* next_devi
       lc.weights_path = cfg.weights;
       lc.max_new_tokens = cfg.maxNew;
       lc.max_ctx = cfg.maxCtx;
+      lc.max_slots = std::max(2, uses);
       return NewLocal(lc, out);
     }
   }
@@ -263,7 +267,8 @@ Error initRegistry(const Config& cfg, Registry* reg) {  // main.go:395-415
   for (size_t i = 0; i < needed.size(); ++i) {
     workers.emplace_back([&, i] {
       int dev = slot[i];
-      errs[i] = createProvider(needed[i], cfg, &dev, &made[i]);
+      const int uses = (int)std::count(cfg.models.begin(), cfg.models.end(), needed[i]) + (needed[i] == cfg.judge ? 1 : 0);
+      errs[i] = createProvider(needed[i], cfg, &dev, uses, &made[i]);
     });
     if (serial) workers.back().join();
   }

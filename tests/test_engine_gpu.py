@@ -114,7 +114,7 @@ def test_teacher_forced_decode_logits(gpu, name, flags):
 WIDE = ["wide-1b", "wide-d128", "wide-mha"]
 
 
-@pytest.mark.parametrize("flags", [0, 64, 32, 4, 68, 36])   # 0: ring kernel, tagged-word hand-overs; 64: ring kernel, grid barriers; 32: register-streaming kernel; 4: bf16 KV
+@pytest.mark.parametrize("flags", [0, 64, 32, 4, 68, 36])   # 0: ring kernel (grid barriers); 64: ring kernel, tagged-word hand-overs; 32: register-streaming kernel; 4: bf16 KV
 @pytest.mark.parametrize("name", WIDE)
 def test_ring_decode_teacher_forced_logits(gpu, name, flags):
     """The persistent decode kernels at hidden = 2048 (the ring kernel's shapes: rows of 2048 / 4096 / 8192
@@ -176,13 +176,44 @@ def test_ring_decode_free_running_matches_register_kernel(gpu, name, chunk):
     e.close()
 
 
+TIES = {"count": 0}     # free-running divergences at oracle near-ties seen in this session (reported, never silent)
+
+
 def greedy_agreement(otoks, olog, gtoks, tol=TOL):
     """Index of the first free-running disagreement that is NOT a numerical tie in the oracle, or -1."""
     for s, (a, b) in enumerate(zip(otoks, gtoks)):
         if a != b:
             margin = float(olog[s][a] - olog[s][b])
-            return (s, margin) if margin > tol else (-2, margin)      # -2: diverged at a tie; stop comparing
+            if margin > tol:
+                return (s, margin)
+            TIES["count"] += 1
+            print("NOTE: free-running divergence at step %d on an oracle near-tie (top-2 margin %.2e <= %.0e); "
+                  "%d such case(s) so far in this session" % (s, margin, tol, TIES["count"]))
+            return (-2, margin)                                        # -2: diverged at a tie
     return (-1, 0.0)
+
+
+def check_batched(o, prompts, firsts, out, lg, n_new, tol=TOL, which=None):
+    """Every sequence of a batched decode call against its own oracle run: greedy tokens (ties excepted, and
+    reported), and the last step's logits.  A sequence that left the oracle's path at a tie is NOT dropped: the
+    oracle is re-run on the GPU's own tokens (teacher forcing) and the last-step logits are compared on that path."""
+    worst, ties = 0.0, 0
+    for i in (which if which is not None else range(len(prompts))):
+        o.reset()
+        otoks, olog = o.generate(prompts[i], n_new + 1, want_logits=True)
+        gt = [firsts[i]] + out[i].tolist()
+        where, margin = greedy_agreement(otoks, olog, gt, tol=tol)
+        assert where < 0, (i, where, margin)
+        if where == -1:
+            want = olog[n_new]
+        else:
+            ties += 1
+            o.reset()
+            want = o.forward(np.concatenate([np.asarray(prompts[i]), np.asarray(gt[:n_new])]), "last")
+        err = float(np.abs(lg[i] - want).max())
+        assert err <= tol, "sequence %d: last-step logits max-abs %.3e (tie path: %s)" % (i, err, where == -2)
+        worst = max(worst, err)
+    return worst, ties
 
 
 @pytest.mark.parametrize("name", ["tiny", "tiny-untied", "small-d128"])
@@ -265,14 +296,8 @@ def test_batched_decode_matches_per_sequence_oracle(gpu, B):
     n_new = 12
     out, lg = e.decode(slots, n_new, want_logits=True)
     o = ref.Oracle(name, seed=4, max_ctx=256)
-    for i, p in enumerate(prompts):
-        o.reset()
-        otoks, olog = o.generate(p, n_new + 1, want_logits=True)
-        gt = [firsts[i]] + out[i].tolist()
-        where, margin = greedy_agreement(otoks, olog, gt)
-        assert where < 0, (i, where, margin)
-        if where == -1:
-            assert np.abs(lg[i] - olog[n_new]).max() <= TOL
+    worst, ties = check_batched(o, prompts, firsts, out, lg, n_new)
+    print("batch %d: worst last-step logit err %.2e, %d sequence(s) checked on their own path after a tie" % (B, worst, ties))
     e.close()
 
 
@@ -385,16 +410,8 @@ def test_wide_batch_decode_full_size_1b(gpu):
         slots.append(s)
         firsts.append(e.prefill(s, p))
     out, lg = e.decode(slots, n_new, want_logits=True)
-    worst = 0.0
-    for i, p in enumerate(prompts):
-        o.reset()
-        otoks, olog = o.generate(p, n_new + 1, want_logits=True)
-        gt = [firsts[i]] + out[i].tolist()
-        where, margin = greedy_agreement(otoks, olog, gt)
-        assert where < 0, (i, where, margin)
-        if where == -1:
-            worst = max(worst, float(np.abs(lg[i] - olog[n_new]).max()))
-    print("wide decode, 1B shape, %d sequences: worst last-step logit err %.3e" % (B, worst))
+    worst, ties = check_batched(o, prompts, firsts, out, lg, n_new)
+    print("wide decode, 1B shape, %d sequences: worst last-step logit err %.3e (%d on their own path after a tie)" % (B, worst, ties))
     assert worst <= TOL
     e.close()
 
@@ -417,14 +434,7 @@ def test_wide_decode_engine_flags(gpu, B, flags):
     out, lg = e.decode(slots, n_new, want_logits=True)
     o = ref.Oracle(name, seed=9, max_ctx=128)
     tol = TOL if not flags & 12 else 8e-2      # reduced-precision storage modes: see test_reduced_precision_modes
-    for i in range(0, B, max(1, B // 6)):
-        o.reset()
-        otoks, olog = o.generate(prompts[i], n_new + 1, want_logits=True)
-        gt = [firsts[i]] + out[i].tolist()
-        where, margin = greedy_agreement(otoks, olog, gt, tol=tol)
-        assert where < 0, (i, where, margin)
-        if where == -1:
-            assert np.abs(lg[i] - olog[n_new]).max() <= tol
+    check_batched(o, prompts, firsts, out, lg, n_new, tol=tol, which=range(0, B, max(1, B // 6)))
     e.close()
 
 
@@ -444,12 +454,5 @@ def test_wide_decode_long_context_two_attention_blocks(gpu):
         firsts.append(e.prefill(s, p))
     n_new = 6
     out, lg = e.decode(slots, n_new, want_logits=True)
-    for i, p in enumerate(prompts):
-        o.reset()
-        otoks, olog = o.generate(p, n_new + 1, want_logits=True)
-        gt = [firsts[i]] + out[i].tolist()
-        where, margin = greedy_agreement(otoks, olog, gt)
-        assert where < 0, (i, where, margin)
-        if where == -1:
-            assert np.abs(lg[i] - olog[n_new]).max() <= TOL
+    check_batched(o, prompts, firsts, out, lg, n_new)
     e.close()

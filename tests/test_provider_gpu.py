@@ -81,3 +81,51 @@ def test_cli_local_timeout_lands_in_warnings(cli):
                        capture_output=True, text=True, timeout=300)
     assert r.returncode == 1
     assert r.stderr == "error: running queries: all models failed: [local-llama-1b-s0: context deadline exceeded]\n"
+
+
+def test_cli_duplicate_model_entries_share_one_engine(cli):
+    """runner.go:62 starts one goroutine per --models entry, duplicates included, against the one provider
+    initRegistry built for the name (main.go:399-403).  Five entries of one local model (which is also the judge)
+    therefore run as five concurrent queries on ONE engine: none may fail for want of a slot, and each answer is
+    the model's answer."""
+    prompt = "What is 2+2?"
+    r = subprocess.run([cli, "--models", ",".join(["local-tiny"] * 5), "--judge", "local-tiny", "--max-new-tokens",
+                        str(NEW), "--json", prompt], capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, r.stderr
+    doc = json.loads(r.stdout)
+    assert "warnings" not in doc and "failed_models" not in doc
+    assert [x["model"] for x in doc["responses"]] == ["local-tiny"] * 5
+    want, margin = oracle_answer(0, prompt)
+    contents = {x["content"] for x in doc["responses"]}
+    if margin > 1e-3:
+        assert contents == {want}
+    rendered = orc.render_judge_prompt(prompt, doc["responses"])
+    consensus, jm = oracle_answer(0, rendered)
+    if jm > 1e-3:
+        assert doc["consensus"] == consensus
+
+
+def test_cli_duplicates_decode_together_on_the_wide_path(cli):
+    """Sixteen entries of the 1B model on one GPU: the provider's scheduler advances all sixteen sequences with one
+    pass over the weights per step, so the fan-out takes a fraction of sixteen queries run one after another."""
+    words = "the quick brown fox jumps over the lazy dog while consensus is computed "
+    prompt = (words * 8)[:511] + "?"
+
+    def fanout_ms(n):
+        env = dict(os.environ, LLMC_BENCH_REPEAT="3", CUDA_VISIBLE_DEVICES="0")
+        r = subprocess.run([cli, "--models", ",".join(["local-llama-1b"] * n), "--judge", "j", "--stub", "j=openai:0:ok",
+                            "--max-new-tokens", "256", "--json", prompt], capture_output=True, text=True, timeout=600, env=env)
+        assert r.returncode == 0, r.stderr[-2000:]
+        doc = json.loads(r.stdout)
+        assert len(doc["responses"]) == n and "warnings" not in doc
+        fans = [float(m.group(1)) for m in re.finditer(r"fan-out ([0-9.]+) ms", r.stderr)]
+        return min(fans[1:]), doc
+
+    one, doc1 = fanout_ms(1)
+    many, doc16 = fanout_ms(16)
+    speedup = 16 * one / many
+    print("one query %.1f ms, sixteen concurrent %.1f ms: %.1fx the serial throughput" % (one, many, speedup))
+    assert speedup >= 4.0
+    same = sum(x["content"] == doc1["responses"][0]["content"] for x in doc16["responses"])
+    print("%d of 16 batched answers are character-identical to the single query's" % same)
+    assert same >= 12          # batch-1 and batched kernels may part ways at a numerical tie, rarely

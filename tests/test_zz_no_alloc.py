@@ -6,8 +6,9 @@ a real-time loop that bans cudaMalloc/cudaFree after start-up.  They pass device
 hold; the kernel's scratch lives in a fixed array inside the library.
 
 Checked here through the C ABI: its logits and tokens equal those of the existing allocating entry
-point (llmc_op_lmhead) on two calls in a row (the second call finds the scratch as the first left it),
-and sizes beyond the compiled-in maximum are refused.  Device buffers come from torch (test plumbing
+point (llmc_op_lmhead) on two calls in a row (the second call finds the scratch as the first left it)
+and, directly, a float64 numpy RMSNorm + matvec of the same inputs; sizes beyond the compiled-in
+maximum are refused.  Device buffers come from torch (test plumbing
 only).  This file sorts last so that a run which stops at the first failure has already run every
 other test."""
 import numpy as np
@@ -44,6 +45,15 @@ def test_noalloc_lmhead_matches_allocating_entry_point_twice(gpu, V, K, B):
         got = dlog.cpu().numpy()
         scale = float(np.sqrt(np.mean(want_logits.astype(np.float64) ** 2)))
         assert np.abs(got - want_logits).max() <= 1e-4 * scale      # the tolerance of the other decode-kernel tests
+        # and against the arithmetic itself, not only against another CUDA entry point
+        x64 = x.astype(np.float64)
+        xn = x64 / np.sqrt((x64 * x64).mean(axis=1, keepdims=True) + 1e-5) * lnp.bf16_to_f32(gain).astype(np.float64)
+        exact = xn @ lnp.bf16_to_f32(W).astype(np.float64).T
+        assert np.abs(got - exact).max() <= 1e-4 * scale
+        margin = np.sort(exact, axis=1)
+        for b in range(B):                                          # argmax, wherever float64 has a clear winner
+            if margin[b, -1] - margin[b, -2] > 1e-4 * scale:
+                assert int(dtok.cpu().numpy()[b]) == int(np.argmax(exact[b]))
         assert dtok.cpu().numpy().tolist() == want_tok.tolist()
         # without a logits buffer the tokens are the same
         dtok2 = torch.full((B,), -7, dtype=torch.int32, device="cuda")
