@@ -3,6 +3,7 @@
 // No counterpart in the reference (/root/reference/internal/provider/provider.go:13-21 is the boundary).
 #pragma once
 #include <cuda.h>
+#include <map>
 #include <mutex>
 #include "common.cuh"
 
@@ -70,6 +71,9 @@ static __device__ __forceinline__ uint64_t make_smem_desc(uint32_t addr) {
          (2ull << 61);
 }
 // instruction descriptor, kind::f16: D fp32, A/B bf16, both K-major, M x N
+// (the A and B format fields are separate, but the hardware wants them equal: an MMA with A = fp16 (field 0) and
+// B = bf16 (field 1) dies with "illegal instruction" on B200 -- tried as a way to carry 11 mantissa bits of the
+// activations in ONE operand instead of the bf16 hi+lo pair)
 __host__ __device__ constexpr uint32_t make_idesc(int m, int n) {
   return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(n >> 3) << 17) | ((uint32_t)(m >> 4) << 24);
 }
@@ -93,17 +97,47 @@ static inline EncodeTiledFn get_encode() {
   return fn;
 }
 
-// 2-D bf16 row-major [rows][cols] tensor, box = [box_rows][64], 128B swizzle
+// 2-D bf16 row-major [rows][cols] tensor, box = [box_rows][64], 128B swizzle.  A descriptor depends only on
+// (pointer, shape, box), and an engine calls with the same few dozen combinations for its whole life (its weight
+// matrices and work buffers), so encoded maps are kept and a launch costs a table lookup instead of three driver
+// calls.  (A freed-and-reused address with the same shape encodes to the same 128 bytes, so stale entries are harmless.)
 static inline bool make_map(CUtensorMap* m, const void* ptr, uint64_t rows, uint64_t cols, uint32_t box_rows) {
+  struct Key {
+    const void* p;
+    uint64_t r, c;
+    uint32_t b;
+    bool operator<(const Key& o) const {
+      if (p != o.p) return p < o.p;
+      if (r != o.r) return r < o.r;
+      if (c != o.c) return c < o.c;
+      return b < o.b;
+    }
+  };
+  static std::map<Key, CUtensorMap> cache;
+  static std::mutex mu;
+  const Key key{ptr, rows, cols, box_rows};
+  {
+    std::lock_guard<std::mutex> lk(mu);
+    auto it = cache.find(key);
+    if (it != cache.end()) {
+      *m = it->second;
+      return true;
+    }
+  }
   EncodeTiledFn enc = get_encode();
   if (!enc) return false;
   cuuint64_t dims[2] = {cols, rows};
   cuuint64_t strides[1] = {cols * 2};
   cuuint32_t box[2] = {64u, box_rows};
   cuuint32_t estr[2] = {1, 1};
-  return enc(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(ptr), dims, strides, box, estr,
-             CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
-             CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+  if (enc(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(ptr), dims, strides, box, estr,
+          CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+          CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) != CUDA_SUCCESS)
+    return false;
+  std::lock_guard<std::mutex> lk(mu);
+  if (cache.size() > 4096) cache.clear();   // bounded: ragged prefill lengths create new row counts
+  cache[key] = *m;
+  return true;
 }
 
 
