@@ -66,7 +66,15 @@ typedef struct llmc_config {
   int32_t prefill_chunk;/* tokens per prefill pass (0 -> 2048) */
   int32_t prefill_impl; /* 0: tcgen05 tensor-core GEMM (product path); 1: plain CUDA-core GEMM (bring-up/comparator) */
   int32_t flags;        /* LLMC_FLAG_* */
+  /* RoPE frequency scaling, Hugging Face rope_type "llama3" (what Llama-3.1 / 3.2 checkpoints declare in
+   * config.json): 0 = none, LLMC_ROPE_LLAMA3 = rescale inv_freq with the four parameters.  With weights_path set
+   * and rope_scaling == 0, a config.json beside the checkpoint is read instead (rope_theta and rope_scaling);
+   * a rope_scaling type other than "default" / "llama3" is refused. */
+  int32_t rope_scaling;
+  float rope_factor, rope_low_freq_factor, rope_high_freq_factor;
+  int32_t rope_original_ctx; /* original_max_position_embeddings */
 } llmc_config;
+#define LLMC_ROPE_LLAMA3 1
 
 #define LLMC_FLAG_NO_GRAPH 1 /* launch decode kernels one by one instead of as a CUDA graph */
 #define LLMC_FLAG_NO_PDL 2   /* no programmatic dependent launch between decode kernels */

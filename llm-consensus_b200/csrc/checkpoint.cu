@@ -289,6 +289,95 @@ struct Loader {
 
 }  // namespace
 
+// ---- config.json beside the checkpoint: only rope_theta and rope_scaling are read.  Real Llama-3.1 / 3.2
+// checkpoints declare rope_scaling {"rope_type": "llama3", "factor", "low_freq_factor", "high_freq_factor",
+// "original_max_position_embeddings"}, which rescales inv_freq at every position; ignoring it would load without
+// error and then disagree with transformers from the first token.
+namespace {
+// position just after `"key"` + ':' at nesting depth 1 of the object starting at s[from] == '{', or npos
+size_t find_key(const std::string& s, size_t from, const std::string& key) {
+  int depth = 0;
+  bool in_str = false;
+  for (size_t i = from; i < s.size(); ++i) {
+    const char c = s[i];
+    if (in_str) {
+      if (c == '\\') ++i;
+      else if (c == '"') in_str = false;
+      continue;
+    }
+    if (c == '"') {
+      if (depth == 1 && s.compare(i + 1, key.size(), key) == 0 && s[i + 1 + key.size()] == '"') {
+        size_t j = i + 2 + key.size();
+        while (j < s.size() && isspace((unsigned char)s[j])) ++j;
+        if (j < s.size() && s[j] == ':') {
+          ++j;
+          while (j < s.size() && isspace((unsigned char)s[j])) ++j;
+          return j;
+        }
+      }
+      in_str = true;
+    } else if (c == '{' || c == '[') {
+      ++depth;
+    } else if (c == '}' || c == ']') {
+      if (--depth == 0) break;
+    }
+  }
+  return std::string::npos;
+}
+bool number_at(const std::string& s, size_t at, double* v) {
+  if (at == std::string::npos) return false;
+  char* end = nullptr;
+  *v = strtod(s.c_str() + at, &end);
+  return end != s.c_str() + at;
+}
+}  // namespace
+
+int read_checkpoint_config(const char* weights_path, RopeScaling* rs, float* rope_theta, std::string* err) {
+  std::string dir = weights_path;
+  struct stat st;
+  if (stat(dir.c_str(), &st) != 0) return LLMC_OK;   // the loader reports a missing path
+  if (!S_ISDIR(st.st_mode)) {
+    const size_t sl = dir.rfind('/');
+    dir = sl == std::string::npos ? "." : dir.substr(0, sl);
+  }
+  const std::string path = dir + "/config.json";
+  FILE* f = fopen(path.c_str(), "rb");
+  if (!f) return LLMC_OK;   // a bare .safetensors file: the caller's llmc_config is all there is
+  std::string js;
+  char buf[4096];
+  size_t n;
+  while ((n = fread(buf, 1, sizeof buf, f)) > 0) js.append(buf, n);
+  fclose(f);
+  const size_t root = js.find('{');
+  if (root == std::string::npos) { *err = path + ": not a JSON object"; return LLMC_ERR_INVALID; }
+  double v;
+  if (number_at(js, find_key(js, root, "rope_theta"), &v)) *rope_theta = (float)v;
+  const size_t at = find_key(js, root, "rope_scaling");
+  if (at == std::string::npos || js.compare(at, 4, "null") == 0) return LLMC_OK;
+  if (js[at] != '{') { *err = path + ": rope_scaling is neither null nor an object"; return LLMC_ERR_INVALID; }
+  size_t ty = find_key(js, at, "rope_type");
+  if (ty == std::string::npos) ty = find_key(js, at, "type");
+  std::string type = "default";
+  if (ty != std::string::npos && js[ty] == '"') type = js.substr(ty + 1, js.find('"', ty + 1) - ty - 1);
+  if (type == "default") return LLMC_OK;
+  if (type != "llama3") {
+    *err = path + ": rope_scaling type \"" + type + "\" is not supported (default, llama3); the checkpoint would load "
+           "but compute different logits than its reference implementation";
+    return LLMC_ERR_INVALID;
+  }
+  double fa, lo, hi, oc;
+  if (!number_at(js, find_key(js, at, "factor"), &fa) || !number_at(js, find_key(js, at, "low_freq_factor"), &lo) ||
+      !number_at(js, find_key(js, at, "high_freq_factor"), &hi) ||
+      !number_at(js, find_key(js, at, "original_max_position_embeddings"), &oc) || hi == lo) {
+    *err = path + ": rope_scaling of type llama3 needs factor, low_freq_factor, high_freq_factor (distinct) and "
+           "original_max_position_embeddings";
+    return LLMC_ERR_INVALID;
+  }
+  rs->kind = LLMC_ROPE_LLAMA3;
+  rs->factor = (float)fa; rs->low_freq_factor = (float)lo; rs->high_freq_factor = (float)hi; rs->original_ctx = (int)oc;
+  return LLMC_OK;
+}
+
 // Fills the weight pointers of an engine whose blob is already allocated and laid out (engine.cu: init_weights).
 int load_checkpoint(llmc_engine* e, const char* path, std::string* err) {
   const ModelDims& d = e->d;

@@ -389,6 +389,17 @@ static int create_impl(llmc_engine* e, const llmc_config& c) {
   e->d = ModelDims{c.hidden, c.layers, c.q_heads, c.kv_heads, c.head_dim, c.inter, c.vocab, c.tied,
                    c.rope_theta, c.rms_eps, c.init_std};
   e->seed = c.seed;
+  if (c.rope_scaling == LLMC_ROPE_LLAMA3) {
+    if (!(c.rope_factor > 0.f) || !(c.rope_low_freq_factor > 0.f) || !(c.rope_high_freq_factor > c.rope_low_freq_factor) ||
+        c.rope_original_ctx < 1)
+      return fail(e, LLMC_ERR_INVALID, "rope_scaling llama3 needs factor > 0, 0 < low_freq_factor < high_freq_factor and original_ctx >= 1");
+    e->rope = RopeScaling{LLMC_ROPE_LLAMA3, c.rope_factor, c.rope_low_freq_factor, c.rope_high_freq_factor, c.rope_original_ctx};
+  } else if (c.rope_scaling != 0) {
+    return fail(e, LLMC_ERR_INVALID, "unknown rope_scaling id");
+  } else if (c.weights_path) {
+    std::string err;   // the checkpoint's own config.json decides, when it exists
+    if (int rc = read_checkpoint_config(c.weights_path, &e->rope, &e->d.rope_theta, &err)) return fail(e, rc, "weights_path: " + err);
+  }
   e->max_slots = c.max_slots; e->max_ctx = c.max_ctx; e->page_size = c.page_size;
   e->prefill_chunk = c.prefill_chunk; e->prefill_impl = c.prefill_impl;
   e->use_graph = !(c.flags & LLMC_FLAG_NO_GRAPH);
@@ -453,7 +464,18 @@ static int create_impl(llmc_engine* e, const llmc_config& c) {
     std::vector<float> hc((size_t)e->max_ctx * (D / 2)), hs((size_t)e->max_ctx * (D / 2));
     for (int p = 0; p < e->max_ctx; ++p)
       for (int i = 0; i < D / 2; ++i) {
-        const double inv = pow((double)d.rope_theta, -2.0 * i / (double)D);
+        double inv = pow((double)d.rope_theta, -2.0 * i / (double)D);
+        if (e->rope.kind == LLMC_ROPE_LLAMA3) {
+          // transformers' _compute_llama3_parameters: wavelengths beyond original_ctx / low_freq_factor are stretched
+          // by `factor`, those below original_ctx / high_freq_factor kept, the band between interpolated
+          const double wavelen = 6.283185307179586476925286766559 / inv, oc = (double)e->rope.original_ctx;
+          const double lo = (double)e->rope.low_freq_factor, hi = (double)e->rope.high_freq_factor;
+          if (wavelen > oc / lo) inv = inv / (double)e->rope.factor;
+          else if (!(wavelen < oc / hi)) {
+            const double smooth = (oc / wavelen - lo) / (hi - lo);
+            inv = (1.0 - smooth) * inv / (double)e->rope.factor + smooth * inv;
+          }
+        }
         const double a = (double)p * inv;
         hc[(size_t)p * (D / 2) + i] = (float)cos(a);
         hs[(size_t)p * (D / 2) + i] = (float)sin(a);

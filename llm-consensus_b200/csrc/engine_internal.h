@@ -20,11 +20,20 @@ struct llmc_engine;
 namespace llmc {
 // checkpoint.cu: fill the (already laid out) weight blob from a safetensors file or directory of shards
 int load_checkpoint(llmc_engine* e, const char* path, std::string* err);
+// RoPE frequency scaling (Hugging Face rope_type "llama3"); kind 0 = none
+struct RopeScaling {
+  int kind = 0;
+  float factor = 1.f, low_freq_factor = 1.f, high_freq_factor = 4.f;
+  int original_ctx = 8192;
+};
+// checkpoint.cu: rope_theta / rope_scaling from the config.json beside a checkpoint (absent file: nothing changes)
+int read_checkpoint_config(const char* weights_path, RopeScaling* rs, float* rope_theta, std::string* err);
 }  // namespace llmc
 
 struct llmc_engine {
   int device = 0;
   llmc::ModelDims d{};
+  llmc::RopeScaling rope{};
   uint64_t seed = 0;
   int max_slots = 8, max_ctx = 8192, page_size = 64, prefill_chunk = 2048, prefill_impl = 0;
   bool use_graph = true, use_pdl = true;

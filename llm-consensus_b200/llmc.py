@@ -34,7 +34,9 @@ class Config(C.Structure):
                [(n, C.c_int32) for n in ("hidden", "layers", "q_heads", "kv_heads", "head_dim", "inter", "vocab", "tied")] + \
                [("rope_theta", C.c_float), ("rms_eps", C.c_float), ("init_std", C.c_float), ("seed", C.c_uint64),
                 ("weights_path", C.c_char_p)] + \
-               [(n, C.c_int32) for n in ("max_slots", "max_ctx", "page_size", "prefill_chunk", "prefill_impl", "flags")]
+               [(n, C.c_int32) for n in ("max_slots", "max_ctx", "page_size", "prefill_chunk", "prefill_impl", "flags")] + \
+               [("rope_scaling", C.c_int32), ("rope_factor", C.c_float), ("rope_low_freq_factor", C.c_float),
+                ("rope_high_freq_factor", C.c_float), ("rope_original_ctx", C.c_int32)]
 
 
 class Stats(C.Structure):
@@ -107,11 +109,15 @@ class Engine:
 
     def __init__(self, shape=SHAPE_LLAMA_1B, device=0, seed=0, max_slots=8, max_ctx=8192, page_size=64,
                  prefill_chunk=2048, prefill_impl=0, flags=0, dims=None, rope_theta=0.0, rms_eps=0.0, init_std=0.0,
-                 weights_path=None):
+                 weights_path=None, rope_llama3=None):
+        """rope_llama3: None, or (factor, low_freq_factor, high_freq_factor, original_max_position_embeddings)."""
         cfg = Config(device=device, shape=shape, seed=seed, max_slots=max_slots, max_ctx=max_ctx,
                      page_size=page_size, prefill_chunk=prefill_chunk, prefill_impl=prefill_impl, flags=flags,
                      rope_theta=rope_theta, rms_eps=rms_eps, init_std=init_std,
                      weights_path=weights_path.encode() if weights_path else None)
+        if rope_llama3 is not None:
+            cfg.rope_scaling, cfg.rope_factor, cfg.rope_low_freq_factor, cfg.rope_high_freq_factor = 1, *map(float, rope_llama3[:3])
+            cfg.rope_original_ctx = int(rope_llama3[3])
         if dims:
             cfg.shape = SHAPE_CUSTOM
             for k, v in dims.items():

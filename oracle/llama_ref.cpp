@@ -47,6 +47,11 @@ typedef struct {
   float rope_theta, rms_eps, init_std;
   uint64_t seed;
   int32_t max_ctx;
+  // RoPE frequency scaling as in Hugging Face's rope_type "llama3" (transformers modeling_rope_utils.py,
+  // _compute_llama3_parameters): 0 = none (rope_type "default"), 1 = llama3 with the four parameters below
+  int32_t rope_scaling;
+  float rope_factor, rope_low_freq_factor, rope_high_freq_factor;
+  int32_t rope_original_ctx;
 } oref_config;
 
 }  // extern "C"
@@ -190,6 +195,19 @@ void* oref_create(const oref_config* cfg) {
   for (int p = 0; p < c.max_ctx; ++p)
     for (int i = 0; i < D / 2; ++i) {
       double inv = pow((double)c.rope_theta, -2.0 * i / (double)D);
+      if (c.rope_scaling == 1) {
+        // wavelengths longer than original_ctx / low_freq_factor are stretched by `factor`, those shorter than
+        // original_ctx / high_freq_factor are kept, the band between is interpolated
+        const double two_pi = 6.283185307179586476925286766559;
+        const double wavelen = two_pi / inv, oc = (double)c.rope_original_ctx;
+        const double lo_w = oc / (double)c.rope_low_freq_factor, hi_w = oc / (double)c.rope_high_freq_factor;
+        if (wavelen > lo_w) inv = inv / (double)c.rope_factor;
+        else if (!(wavelen < hi_w)) {
+          const double smooth = (oc / wavelen - (double)c.rope_low_freq_factor) /
+                                ((double)c.rope_high_freq_factor - (double)c.rope_low_freq_factor);
+          inv = (1.0 - smooth) * inv / (double)c.rope_factor + smooth * inv;
+        }
+      }
       double a = (double)p * inv;
       m->rope_cos[(size_t)p * (D / 2) + i] = (float)cos(a);
       m->rope_sin[(size_t)p * (D / 2) + i] = (float)sin(a);

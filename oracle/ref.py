@@ -48,7 +48,10 @@ class Config(C.Structure):
     _fields_ = [(n, C.c_int32) for n in
                 ("hidden", "layers", "q_heads", "kv_heads", "head_dim", "inter", "vocab", "tied")] + \
                [("rope_theta", C.c_float), ("rms_eps", C.c_float), ("init_std", C.c_float),
-                ("seed", C.c_uint64), ("max_ctx", C.c_int32)]
+                ("seed", C.c_uint64), ("max_ctx", C.c_int32),
+                # HF rope_type "llama3" (0 = off): factor, low/high frequency factors, original context
+                ("rope_scaling", C.c_int32), ("rope_factor", C.c_float), ("rope_low_freq_factor", C.c_float),
+                ("rope_high_freq_factor", C.c_float), ("rope_original_ctx", C.c_int32)]
 
 
 def build(force=False):
@@ -83,9 +86,14 @@ def lib():
     return _lib
 
 
-def make_config(shape="tiny", seed=0, max_ctx=1024, rope_theta=500000.0, rms_eps=1e-5, init_std=0.02, **over):
+def make_config(shape="tiny", seed=0, max_ctx=1024, rope_theta=500000.0, rms_eps=1e-5, init_std=0.02, rope_llama3=None,
+                **over):
+    """rope_llama3: None, or (factor, low_freq_factor, high_freq_factor, original_max_position_embeddings)."""
     d = dict(SHAPES[shape]) if isinstance(shape, str) else dict(shape)
     d.update(over)
+    if rope_llama3 is not None:
+        f, lo, hi, oc = rope_llama3
+        d.update(rope_scaling=1, rope_factor=f, rope_low_freq_factor=lo, rope_high_freq_factor=hi, rope_original_ctx=int(oc))
     return Config(rope_theta=rope_theta, rms_eps=rms_eps, init_std=init_std, seed=seed, max_ctx=max_ctx, **d)
 
 

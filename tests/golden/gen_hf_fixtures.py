@@ -20,7 +20,10 @@ sys.path.insert(0, os.path.join(HERE, "..", ".."))
 from oracle import ref, llama_np as lnp  # noqa: E402
 
 
-def hf_logits(name, seed, n_tok):
+LLAMA3_ROPE = (8.0, 1.0, 4.0, 64)   # factor, low_freq_factor, high_freq_factor, original_max_position_embeddings
+
+
+def hf_logits(name, seed, n_tok, rope_llama3=None):
     import torch
     from transformers import LlamaConfig, LlamaForCausalLM
     s = ref.SHAPES[name]
@@ -30,6 +33,10 @@ def hf_logits(name, seed, n_tok):
                       rope_theta=500000.0, tie_word_embeddings=bool(s["tied"]), attention_bias=False,
                       mlp_bias=False, max_position_embeddings=256)
     cfg.rope_parameters = {"rope_type": "default", "rope_theta": 500000.0}
+    if rope_llama3 is not None:   # the scaling real Llama-3.1 / 3.2 checkpoints declare in config.json
+        f, lo, hi, oc = rope_llama3
+        cfg.rope_parameters = {"rope_type": "llama3", "rope_theta": 500000.0, "factor": f, "low_freq_factor": lo,
+                               "high_freq_factor": hi, "original_max_position_embeddings": oc}
     hf = LlamaForCausalLM(cfg).float().eval()
     H, D = s["hidden"], s["head_dim"]
     QD, KD, I, V = s["q_heads"] * D, s["kv_heads"] * D, s["inter"], s["vocab"]
@@ -61,6 +68,12 @@ def main():
         toks, lg = hf_logits(name, seed, n_tok)
         np.savez_compressed(os.path.join(HERE, "hf_%s.npz" % name), tokens=toks, logits=lg, seed=seed)
         print(name, lg.shape, float(lg.std()))
+    # RoPE frequency scaling (rope_type "llama3"): 200 positions against an original context of 64, so the three
+    # bands (kept / interpolated / stretched) all occur among the 16 frequencies of the tiny shape
+    toks, lg = hf_logits("tiny", 6, 200, LLAMA3_ROPE)
+    np.savez_compressed(os.path.join(HERE, "hf_tiny_rope_llama3.npz"), tokens=toks, logits=lg, seed=6,
+                        rope_llama3=np.asarray(LLAMA3_ROPE, np.float64))
+    print("tiny + llama3 rope", lg.shape, float(lg.std()))
     kat = {}
     for seed, layer, kind, rows, cols in [(0, -1, 0, 4, 8), (0, 3, 1, 2, 16), (12345, 0, 8, 3, 8), (7, 15, 6, 2, 8)]:
         m = lnp.matrix(seed, lnp.tensor_id(layer, kind), rows, cols)

@@ -416,6 +416,88 @@ def test_wide_batch_decode_full_size_1b(gpu):
     e.close()
 
 
+GOLDEN = os.path.join(ROOT, "tests", "golden")
+
+
+def fixture_err(lg_row, probe_idx, probe_val, top_idx, top_val):
+    """max-abs difference of one GPU logit row against the oracle values a committed fixture holds for it: the logits
+    at 512 fixed vocabulary positions and the oracle's top 16."""
+    return max(float(np.abs(lg_row[probe_idx] - probe_val).max()), float(np.abs(lg_row[top_idx] - top_val).max()))
+
+
+@pytest.mark.parametrize("B", [32, 128])
+def test_wide_batch_decode_full_size_1b_b32_b128(gpu, B):
+    """BASELINE.json configs[4]'s 1B points at B = 32 and 128 (contexts 512-560): the tcgen05 decode GEMMs of the wide
+    path -- gemm_decode_tc.cu up to 32 sequences, gemm_tcgen05.cu in decode mode with split-K above -- at the full
+    Llama-3.2-1B shape.  Three sequences of each batch are checked against their own fp32 oracle run, replayed from
+    tests/golden/oracle_1b_wide.npz (generator: tests/golden/gen_oracle_1b_wide_fixture.py, which also defines the
+    prompts)."""
+    path = os.path.join(GOLDEN, "oracle_1b_wide.npz")
+    if not os.path.exists(path):
+        pytest.fail("fixture %s is missing; run tests/golden/gen_oracle_1b_wide_fixture.py" % path)
+    sys.path.insert(0, GOLDEN)
+    import gen_oracle_1b_wide_fixture as gen
+    fx = np.load(path)
+    n_new = int(fx["n_new"])
+    prompts = gen.prompts_for(B)
+    e = gpu.Engine(shape=gpu.SHAPE_LLAMA_1B, seed=0, max_ctx=640, max_slots=B, prefill_impl=DEFAULT_IMPL)
+    slots, firsts = [], []
+    for p in prompts:
+        s = e.seq_alloc()
+        slots.append(s)
+        firsts.append(e.prefill(s, p))
+    out, lg = e.decode(slots, n_new, want_logits=True)
+    worst, ties = 0.0, 0
+    for i in gen.CHECK[B]:
+        otoks, margins = fx["b%d_s%d_tokens" % (B, i)], fx["b%d_s%d_margins" % (B, i)]
+        gt = [firsts[i]] + out[i].tolist()
+        same_path = True
+        for s_, (a, b) in enumerate(zip(otoks.tolist(), gt)):
+            if a != b:
+                assert margins[s_] <= TOL, "sequence %d diverges at step %d where the oracle margin is %.3e" % (i, s_, margins[s_])
+                print("NOTE: B=%d sequence %d left the oracle's path at step %d on a near-tie (margin %.2e)" % (B, i, s_, margins[s_]))
+                same_path, ties = False, ties + 1
+                break
+        if same_path:
+            err = fixture_err(lg[i], fx["probe_idx"], fx["b%d_s%d_probe" % (B, i)], fx["b%d_s%d_top_idx" % (B, i)],
+                              fx["b%d_s%d_top_val" % (B, i)])
+            assert err <= TOL, "sequence %d: last-step logits differ by %.3e" % (i, err)
+            worst = max(worst, err)
+    print("wide decode, 1B shape, B=%d, contexts 512-566: worst checked logit err %.3e, %d tie(s)" % (B, worst, ties))
+    assert ties < len(gen.CHECK[B])
+    e.close()
+
+
+def test_llama8b_2048_prompt_fixture(gpu):
+    """BASELINE.json configs[3]'s model at its prompt length: the Llama-3-8B shape, 2 048-token prompt (one full
+    prefill chunk, 32 key tiles per head in the tensor-core prefill attention), then 64 decode steps teacher-forced on
+    the oracle's tokens (contexts 2 049..2 112: the decode attention runs split over several blocks).  The fp32 oracle
+    run (tens of CPU-minutes) is replayed from tests/golden/oracle_8b_2048.npz (tests/golden/gen_oracle_8b_fixture.py)."""
+    path = os.path.join(GOLDEN, "oracle_8b_2048.npz")
+    if not os.path.exists(path):
+        pytest.fail("fixture %s is missing; run tests/golden/gen_oracle_8b_fixture.py" % path)
+    fx = np.load(path)
+    n_prompt, otoks = int(fx["n_prompt"]), fx["tokens"]
+    prompt = np.random.default_rng(int(fx["prompt_seed"])).integers(0, 128256, n_prompt).astype(np.int32)
+    e = gpu.Engine(shape=gpu.SHAPE_LLAMA_8B, seed=0, max_ctx=n_prompt + len(otoks) + 8, max_slots=1, prefill_impl=DEFAULT_IMPL)
+    slot = e.seq_alloc()
+    nxt, lg = e.prefill(slot, prompt, want_logits=True)
+    errs = [fixture_err(lg, fx["probe_idx"], fx["probe_val"][0], fx["top_idx"][0], fx["top_val"][0])]
+    margin = fx["top_val"][:, 0] - fx["top_val"][:, 1]
+    agree = int(nxt == otoks[0])
+    assert nxt == otoks[0] or margin[0] <= TOL
+    for s_ in range(1, len(otoks)):
+        e.set_next_token(slot, int(otoks[s_ - 1]))
+        out, lg = e.decode([slot], 1, want_logits=True)
+        errs.append(fixture_err(lg[0], fx["probe_idx"], fx["probe_val"][s_], fx["top_idx"][s_], fx["top_val"][s_]))
+        agree += int(out[0, 0] == otoks[s_])
+        assert out[0, 0] == otoks[s_] or margin[s_] <= TOL, "step %d: argmax differs where the oracle margin is %.3e" % (s_, margin[s_])
+    print("8B shape, 2048-token prompt + %d teacher-forced steps: worst logit err %.3e (prefill %.3e), argmax agreement %d/%d, "
+          "logit std %.3f" % (len(otoks) - 1, max(errs), errs[0], agree, len(otoks), float(fx["logit_std"])))
+    assert max(errs) <= TOL
+    e.close()
+
+
 @pytest.mark.parametrize("flags", [1, 2, 3, 4, 8, 12])   # no graph, no PDL, both, bf16 KV, single-bf16 operands, both
 @pytest.mark.parametrize("B", [5, 40])
 def test_wide_decode_engine_flags(gpu, B, flags):

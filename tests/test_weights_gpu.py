@@ -116,3 +116,63 @@ def test_cli_weights_flag(gpu, tmp_path):
         import json
         outs.append(json.load(open(out))["responses"][0]["content"])
     assert outs[0] == outs[1] and len(outs[0]) > 0
+
+
+ROPE3 = (8.0, 1.0, 4.0, 64)       # factor, low_freq_factor, high_freq_factor, original_max_position_embeddings
+
+
+def test_rope_scaling_llama3_engine_matches_oracle(gpu):
+    """llmc_config.rope_scaling = LLMC_ROPE_LLAMA3: prefill logits at 120 positions and a few decode steps against
+    the oracle with the same scaling (itself pinned to transformers by tests/golden/hf_tiny_rope_llama3.npz)."""
+    dims = DIMS["tiny"]
+    o = ref.Oracle("tiny", seed=41, max_ctx=256, rope_llama3=ROPE3)
+    e = gpu.Engine(dims=dims, seed=41, max_ctx=256, max_slots=1, rope_llama3=ROPE3)
+    toks = np.random.default_rng(8).integers(0, dims["vocab"], 120)
+    otoks, olog = o.generate(toks, 6, want_logits=True)
+    slot = e.seq_alloc()
+    nxt, lg = e.prefill(slot, toks, want_logits=True)
+    assert np.abs(lg - olog[0]).max() <= 2e-2
+    plain = ref.Oracle("tiny", seed=41, max_ctx=256).forward(toks, "last")
+    assert np.abs(lg - plain).max() > 2e-2         # the scaling is visible at this length
+    for s_ in range(1, 6):
+        e.set_next_token(slot, int(otoks[s_ - 1]))
+        _, lgd = e.decode([slot], 1, want_logits=True)
+        assert np.abs(lgd[0] - olog[s_]).max() <= 2e-2
+    e.close()
+
+
+def test_config_json_beside_the_checkpoint_sets_rope_scaling(gpu, tmp_path):
+    """A checkpoint directory whose config.json declares rope_scaling of type llama3 (as Llama-3.1 / 3.2 do) is run
+    with that scaling; a type the library does not implement is refused instead of loading and computing something
+    else."""
+    import json
+    dims = DIMS["tiny"]
+    o = ref.Oracle("tiny", seed=42, max_ctx=256, rope_llama3=ROPE3)
+    d = tmp_path / "ckpt"
+    d.mkdir()
+    write_safetensors(str(d / "model.safetensors"), hf_tensors(o, dims))
+    cfg = {"architectures": ["LlamaForCausalLM"], "rope_theta": 500000.0, "nested": {"rope_scaling": "decoy"},
+           "rope_scaling": {"factor": ROPE3[0], "low_freq_factor": ROPE3[1], "high_freq_factor": ROPE3[2],
+                            "original_max_position_embeddings": ROPE3[3], "rope_type": "llama3"}}
+    (d / "config.json").write_text(json.dumps(cfg, indent=2))
+    toks = np.random.default_rng(9).integers(0, dims["vocab"], 120)
+    want = o.forward(toks, "last")
+    for path in (str(d), str(d / "model.safetensors")):      # directory, or the file inside it
+        e = gpu.Engine(dims=dims, seed=1, max_ctx=256, max_slots=1, weights_path=path)
+        slot = e.seq_alloc()
+        _, lg = e.prefill(slot, toks, want_logits=True)
+        assert np.abs(lg - want).max() <= 2e-2
+        e.close()
+    cfg["rope_scaling"] = {"rope_type": "yarn", "factor": 4.0}
+    (d / "config.json").write_text(json.dumps(cfg))
+    with pytest.raises(gpu.LlmcError) as ei:
+        gpu.Engine(dims=dims, seed=1, max_ctx=256, max_slots=1, weights_path=str(d))
+    assert "yarn" in str(ei.value) and "rope_scaling" in str(ei.value)
+    cfg["rope_scaling"] = None
+    (d / "config.json").write_text(json.dumps(cfg))
+    e = gpu.Engine(dims=dims, seed=1, max_ctx=256, max_slots=1, weights_path=str(d))      # null: plain RoPE
+    slot = e.seq_alloc()
+    _, lg = e.prefill(slot, toks, want_logits=True)
+    o2 = ref.Oracle("tiny", seed=42, max_ctx=256)
+    assert np.abs(lg - o2.forward(toks, "last")).max() <= 2e-2
+    e.close()
