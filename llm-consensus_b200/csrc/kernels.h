@@ -155,8 +155,9 @@ cudaError_t launch_rope_append(const float* qkv, int T, int p0, int slot, const 
                                void* vpool, int kv_fp32, int page_size, int q_heads, int kv_heads, int head_dim,
                                float* q_out, cudaStream_t s);
 // causal attention of T new rows (positions p0..p0+T-1) over the paged cache; out bf16 [T][qd] (hi, lo).
-// impl 0: tensor-core kernel (prefill_attn_mma.cu) whenever the shape allows it and a workspace is given, else the
-// CUDA-core kernel; impl 1: always the CUDA-core kernel (comparator).
+// impl 0: tensor-core kernel whenever the shape allows it and a workspace is given -- tcgen05 (prefill_attn_tc.cu) for
+// head sizes 64 / 128, else mma.sync (prefill_attn_mma.cu) -- else the CUDA-core kernel; impl 1: always the CUDA-core
+// kernel (comparator); impl 2: the mma.sync kernel (comparator).
 cudaError_t launch_prefill_attention(const float* q, int T, int p0, int slot, const int* block_table,
                                      int bt_stride, const void* kpool, const void* vpool, int kv_fp32, int page_size,
                                      int q_heads, int kv_heads, int head_dim, uint16_t* out_hi, uint16_t* out_lo,
@@ -169,6 +170,15 @@ cudaError_t launch_prefill_attention_mma(const float* q, int T, int p0, int slot
                                          int bt_stride, const void* kpool, const void* vpool, int kv_fp32,
                                          int page_size, int q_heads, int kv_heads, int head_dim, uint16_t* out_hi,
                                          uint16_t* out_lo, uint16_t* workspace, cudaStream_t s);
+
+// ------------------------------------------------------------------ prefill_attn_tc.cu
+// the same attention on the 5th-generation tensor cores (tcgen05.mma, S / PV accumulators in TMEM, K and V^T tiles by TMA);
+// same arguments and workspace size as the mma.sync version (the workspace layout differs: V planes are transposed)
+bool prefill_attn_tc_supported(int head_dim, int G);
+cudaError_t launch_prefill_attention_tc(const float* q, int T, int p0, int slot, const int* block_table,
+                                        int bt_stride, const void* kpool, const void* vpool, int kv_fp32,
+                                        int page_size, int q_heads, int kv_heads, int head_dim, uint16_t* out_hi,
+                                        uint16_t* out_lo, uint16_t* workspace, cudaStream_t s);
 
 // ------------------------------------------------------------------ decode_wide.cu (decode, 9..128 sequences)
 cudaError_t launch_embed_slots(const uint16_t* emb, const int* next_token, const int* slots, int B, int H, float* x,

@@ -370,7 +370,7 @@ int llmc_op_prefill_attention(int device, int T, int p0, int q_heads, int kv_hea
   O_TRY(pool.get(&dbt, bt.size(), bt.data()));
   O_TRY(launch_rope_append(dqkv, T, p0, 0, dc, ds, dbt, pps, dk, dv, kv_fp32, page_size, q_heads, kv_heads, D, dq, 0));
   uint16_t* dws = nullptr;
-  if (impl == 0 && q_heads % kv_heads == 0 && prefill_attn_mma_supported(D, q_heads / kv_heads))
+  if ((impl == 0 || impl == 2) && q_heads % kv_heads == 0 && prefill_attn_mma_supported(D, q_heads / kv_heads))
   {
     const size_t wsb = prefill_attn_mma_workspace_bytes(total, kv_heads, D);
     O_TRY(pool.get(&dws, wsb / 2));

@@ -8,6 +8,9 @@
 //
 // No counterpart in the reference (/root/reference/internal/provider/provider.go:13-21 is the
 // boundary; the providers behind it are remote HTTP calls).
+#include <stdlib.h>
+#include <string.h>
+
 #include "common.cuh"
 #include "kernels.h"
 #include "attn_common.cuh"
@@ -268,6 +271,14 @@ cudaError_t launch_prefill_attention(const float* q, int T, int p0, int slot, co
                                      uint16_t* mma_workspace, int impl, cudaStream_t s) {
   if (q_heads % kv_heads != 0 || page_size % ATT_TP != 0) return cudaErrorInvalidValue;
   const int G = q_heads / kv_heads;
+  // tensor-core paths: tcgen05 (prefill_attn_tc.cu) where the shape allows it, else mma.sync (prefill_attn_mma.cu);
+  // LLMC_PREFILL_ATTN=mma / tc forces one of them (comparison runs)
+  static const char* const pick = getenv("LLMC_PREFILL_ATTN");
+  const bool want_tc = pick ? strcmp(pick, "mma") != 0 : true;
+  if (impl == 2) impl = 0;   // 2 = the mma.sync kernel (comparator of the tests), otherwise handled like 0
+  else if (impl == 0 && mma_workspace && want_tc && prefill_attn_tc_supported(head_dim, G))
+    return launch_prefill_attention_tc(q, T, p0, slot, block_table, bt_stride, kpool, vpool, kv_fp32, page_size,
+                                       q_heads, kv_heads, head_dim, out_hi, out_lo, mma_workspace, s);
   if (impl == 0 && mma_workspace && prefill_attn_mma_supported(head_dim, G))
     return launch_prefill_attention_mma(q, T, p0, slot, block_table, bt_stride, kpool, vpool, kv_fp32, page_size,
                                         q_heads, kv_heads, head_dim, out_hi, out_lo, mma_workspace, s);

@@ -8,13 +8,12 @@ import llm_consensus_b200.llmc as llmc
 
 trace = len(sys.argv) > 1 and sys.argv[1] == "trace"
 variants = [("barriers", {"LLMC_RING_FLOW": "0"}),
-            ("barriers, relaxed poll + fence", {"LLMC_RING_FLOW": "0", "LLMC_RING_POLL": "2"}),
             ("flow, warp sentinel", {"LLMC_RING_FLOW": "1", "LLMC_FLOW_POLL": "0"}),
             ("flow, all threads poll", {"LLMC_RING_FLOW": "1", "LLMC_FLOW_POLL": "1"})]
 extra = os.environ.get("RING_VARIANT_TPB")
 if extra:
     for t in extra.split(","):
-        variants.append(("flow, sentinel, %s tiles/block" % t, {"LLMC_RING_FLOW": "1", "LLMC_FLOW_POLL": "0", "LLMC_MEGA_TILES_PER_BLOCK": t}))
+        variants.append(("barriers, %s attention tiles/block" % t, {"LLMC_RING_FLOW": "0", "LLMC_MEGA_TILES_PER_BLOCK": t}))
 prompt = np.random.default_rng(1).integers(0, 128256, 512)
 ref_toks = None
 for name, env in variants:

@@ -122,7 +122,7 @@ def test_rmsnorm_rows(gpu, T, H):
     assert np.abs(pair - want).max() <= 2 ** -15 * np.abs(want).max() + 1e-6
 
 
-@pytest.mark.parametrize("impl", [0, 1])   # 0: tensor-core kernel where the shape allows it; 1: CUDA-core kernel
+@pytest.mark.parametrize("impl", [0, 1, 2])   # 0: tcgen05 kernel where the shape allows it (else mma.sync); 1: CUDA-core kernel; 2: mma.sync kernel
 @pytest.mark.parametrize("nq,nkv,d", [(8, 2, 32), (32, 8, 64), (4, 2, 128), (4, 4, 64), (16, 4, 128), (8, 1, 64)])
 @pytest.mark.parametrize("T,p0,page", [(1, 0, 64), (20, 0, 32), (70, 0, 64), (9, 100, 64), (130, 61, 32),
                                        (130, 61, 64), (33, 200, 128)])
@@ -175,9 +175,10 @@ def test_prefill_attention_tensor_core_matches_cuda_core(gpu):
         qkv = rng.standard_normal((T, QD + 2 * KD)).astype(np.float32)
         kp = rng.standard_normal((p0, KD)).astype(np.float32)
         vp = rng.standard_normal((p0, KD)).astype(np.float32)
-        res = [gpu.op_prefill_attention(qkv, kp, vp, nq, nkv, d, 64, kv_fp32=True, split=True, impl=i) for i in (0, 1)]
+        res = [gpu.op_prefill_attention(qkv, kp, vp, nq, nkv, d, 64, kv_fp32=True, split=True, impl=i) for i in (0, 1, 2)]
         pair = [lnp.bf16_to_f32(r[0]) + lnp.bf16_to_f32(r[1]) for r in res]
-        assert np.abs(pair[0] - pair[1]).max() <= 2e-5 * np.abs(pair[1]).max()
+        assert np.abs(pair[0] - pair[1]).max() <= 2e-5 * np.abs(pair[1]).max()     # tcgen05 kernel vs CUDA cores
+        assert np.abs(pair[2] - pair[1]).max() <= 2e-5 * np.abs(pair[1]).max()     # mma.sync kernel vs CUDA cores
 
 
 def run_gemm_check(T, N, K, epi, impl, split=0, timeout=120):
