@@ -170,6 +170,18 @@ class Ranks:
     def allsum(self, v):
         return self._reduce(v, "SUM")
 
+    def host_signal(self, key):
+        """Rank 0 marks `key` in the rendezvous store; host_wait() blocks the other ranks on the HOST until then.  (An
+        NCCL barrier would park a spinning kernel on every waiting rank's GPU -- exactly the GPUs the consensus leg of
+        rank 0 is about to use.)"""
+        if self.dist is not None:
+            self.dist.distributed_c10d._get_default_store().set(key, "1")
+
+    def host_wait(self, key):
+        if self.dist is not None:
+            import datetime
+            self.dist.distributed_c10d._get_default_store().wait([key], datetime.timedelta(seconds=1800))
+
     def close(self):
         if self.dist is not None:
             self.dist.destroy_process_group()
@@ -331,6 +343,8 @@ def run_ours(args, rank, world, local_rank):
     }
     eng.close()
     barrier()
+    if rank != 0:
+        ranks.host_wait("extra_legs_done")      # idle on the host, GPUs free, while rank 0 runs the extra legs
     if rank == 0 and not args.no_extra:
         # extra legs, outside the timed region (other ranks have released their GPUs at the barrier above)
         line["decode_8b"] = decode_8b_leg(llmc, local_rank, peak)
@@ -341,6 +355,7 @@ def run_ours(args, rank, world, local_rank):
         line["cpu_baseline"], _ = cpu_sample()
     if rank == 0:
         print(json.dumps(line), flush=True)
+        ranks.host_signal("extra_legs_done")
     barrier()
     ranks.close()
 

@@ -23,6 +23,15 @@ def test_two_rank_aggregation_with_gloo(tmp_path):
         ranks.barrier()
         # rank r: prefill 10 + 5 r ms, decode 90 + 45 r ms, wall 0.2 + 0.1 r s, 81 * 255 launches, 1 step
         agg = bench.aggregate(ranks, 10.0 + 5.0 * rank, 90.0 + 45.0 * rank, 0.2 + 0.1 * rank, 81 * 255, 1)
+        # the host-side hand-shake that keeps the other ranks off their GPUs while rank 0 runs its extra legs
+        import time
+        t0 = time.time()
+        if rank == 0:
+            time.sleep(0.5)
+            ranks.host_signal("extra_legs_done")
+        else:
+            ranks.host_wait("extra_legs_done")
+            assert time.time() - t0 >= 0.4
         if rank == 0:
             print(json.dumps(dict(agg, n_gpus=world)))
         ranks.close()
