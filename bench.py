@@ -215,7 +215,10 @@ def consensus_leg(n_gpus, passes=3):
         open(pf, "w").write(prompt)
         cmd = [cli, "--models", models, "--judge", "local-llama-1b-s0", "--file", pf, "--output", out,
                "--max-new-tokens", str(NEW_TOKENS), "--max-ctx", "8192", "--timeout", "600", "--quiet"]
-        env = dict(os.environ, LLMC_BENCH_REPEAT=str(passes), CUDA_VISIBLE_DEVICES=",".join(str(i) for i in range(n_gpus)))
+        # the first n_gpus devices this process can see (an inherited CUDA_VISIBLE_DEVICES is narrowed, not replaced)
+        seen = [d for d in os.environ.get("CUDA_VISIBLE_DEVICES", "").split(",") if d.strip()]
+        devs = seen[:n_gpus] if len(seen) >= n_gpus else [str(i) for i in range(n_gpus)]
+        env = dict(os.environ, LLMC_BENCH_REPEAT=str(passes), CUDA_VISIBLE_DEVICES=",".join(devs))
         try:
             r = subprocess.run(cmd, env=env, capture_output=True, text=True, timeout=600)
         except subprocess.TimeoutExpired:

@@ -430,6 +430,13 @@ static int create_impl(llmc_engine* e, const llmc_config& c) {
                   decode_flow_supported(e->d.hidden, e->d.qd(), e->d.kd(), e->d.inter, e->d.vocab, e->d.q_heads,
                                         e->d.kv_heads, e->d.head_dim, e->prop.multiProcessorCount);
   }
+  {
+    const char* rm = getenv("LLMC_RING_MMA");
+    const bool want = rm ? atoi(rm) != 0 : (c.flags & LLMC_FLAG_RING_MMA) != 0;
+    e->use_ring_mma = e->use_ring && !e->use_flow && want && e->d.hidden / 8 <= 2 * e->prop.multiProcessorCount &&
+                      decode_ring_mma_supported(e->d.hidden, e->d.qd(), e->d.kd(), e->d.inter, e->d.vocab, e->d.q_heads,
+                                                e->d.kv_heads, e->d.head_dim);
+  }
   e->stats.sm_count = e->prop.multiProcessorCount; e->stats.cc_major = e->prop.major; e->stats.cc_minor = e->prop.minor;
   E_TRY(cudaStreamCreateWithFlags(&e->stream, cudaStreamNonBlocking));
   E_TRY(cudaEventCreate(&e->ev0));
@@ -559,7 +566,7 @@ static int create_impl(llmc_engine* e, const llmc_config& c) {
   stage("workspaces, sync");
   if (init_trace)
     fprintf(stderr, "[init dev %d] batch-1 decode path: %s\n", c.device,
-            !e->use_mega ? "kernel graph" : e->use_flow ? "decode_flow (ring, tagged-word hand-overs)"
+            !e->use_mega ? "kernel graph" : e->use_flow ? "decode_flow (ring, tagged-word hand-overs)" : e->use_ring_mma ? "decode_ring_mma (ring, mma.sync slots)"
                                           : e->use_ring ? "decode_ring (ring, grid barriers)" : "decode_mega (register streaming)");
   e->stats.graph_enabled = e->use_graph;
   e->stats.pdl_enabled = e->use_pdl;
@@ -779,7 +786,8 @@ static int decode_group(llmc_engine* e, const int32_t* slots, int32_t nslots, in
       const char* fp = getenv("LLMC_FLOW_POLL");
       m.flow_poll_mode = fp ? atoi(fp) : 0;
       E_TRY(launch_decode_flow(m, e->prop.multiProcessorCount, s));
-    } else if (e->use_ring) E_TRY(launch_decode_ring(m, e->prop.multiProcessorCount, s));
+    } else if (e->use_ring_mma) E_TRY(launch_decode_ring_mma(m, e->prop.multiProcessorCount, s));
+    else if (e->use_ring) E_TRY(launch_decode_ring(m, e->prop.multiProcessorCount, s));
     else E_TRY(launch_decode_mega(m, e->prop.multiProcessorCount, s));
     e->stats.kernel_launches += 1;
   }

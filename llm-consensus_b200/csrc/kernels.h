@@ -135,6 +135,10 @@ cudaError_t launch_decode_mega(const MegaArgs& a, int sm_count, cudaStream_t s);
 // same contract as launch_decode_mega; weights travel through a per-SM shared-memory ring filled by TMA bulk copies
 bool decode_ring_supported(int H, int QD, int KD, int I, int V, int q_heads, int kv_heads, int head_dim);
 cudaError_t launch_decode_ring(const MegaArgs& a, int sm_count, cudaStream_t s);
+// ------------------------------------------------------------------ decode_ring_mma.cu
+// the ring kernel with the slot arithmetic on mma.sync (weights = B operand, activation = hi / mid / lo rows of A)
+bool decode_ring_mma_supported(int H, int QD, int KD, int I, int V, int q_heads, int kv_heads, int head_dim);
+cudaError_t launch_decode_ring_mma(const MegaArgs& a, int sm_count, cudaStream_t s);
 // ------------------------------------------------------------------ decode_flow.cu
 // the ring kernel without grid barriers: every activation travels as an 8-byte (value, tag) word that its readers
 // poll, so a phase hand-over costs one store-to-load trip through L2 instead of fence + arrive + poll + reload

@@ -8,6 +8,7 @@ import llm_consensus_b200.llmc as llmc
 
 trace = len(sys.argv) > 1 and sys.argv[1] == "trace"
 variants = [("barriers", {"LLMC_RING_FLOW": "0"}),
+            ("barriers, mma.sync slots", {"LLMC_RING_FLOW": "0", "LLMC_RING_MMA": "1"}),
             ("flow, warp sentinel", {"LLMC_RING_FLOW": "1", "LLMC_FLOW_POLL": "0"}),
             ("flow, all threads poll", {"LLMC_RING_FLOW": "1", "LLMC_FLOW_POLL": "1"})]
 extra = os.environ.get("RING_VARIANT_TPB")
@@ -17,7 +18,7 @@ if extra:
 prompt = np.random.default_rng(1).integers(0, 128256, 512)
 ref_toks = None
 for name, env in variants:
-    for k in ("LLMC_RING_FLOW", "LLMC_FLOW_POLL", "LLMC_RING_POLL", "LLMC_MEGA_TILES_PER_BLOCK", "LLMC_MEGA_TRACE"):
+    for k in ("LLMC_RING_FLOW", "LLMC_FLOW_POLL", "LLMC_RING_POLL", "LLMC_RING_MMA", "LLMC_MEGA_TILES_PER_BLOCK", "LLMC_MEGA_TRACE"):
         os.environ.pop(k, None)
     os.environ.update(env)
     if trace:
