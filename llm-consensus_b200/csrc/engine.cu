@@ -437,6 +437,14 @@ static int create_impl(llmc_engine* e, const llmc_config& c) {
                       decode_ring_mma_supported(e->d.hidden, e->d.qd(), e->d.kd(), e->d.inter, e->d.vocab, e->d.q_heads,
                                                 e->d.kv_heads, e->d.head_dim);
   }
+  {
+    // 2..4 sequences per decode call: the batched ring kernel unless LLMC_FLAG_NO_RING_BATCH / LLMC_RING_BATCH=0
+    const char* rb = getenv("LLMC_RING_BATCH");
+    const bool want = rb ? atoi(rb) != 0 : (c.flags & LLMC_FLAG_NO_RING_BATCH) == 0;
+    e->use_ringb = e->use_mega && !(c.flags & LLMC_FLAG_NO_RING) && want &&
+                   decode_ring_batch_supported(2, e->d.hidden, e->d.qd(), e->d.kd(), e->d.inter, e->d.vocab, e->d.q_heads,
+                                               e->d.kv_heads, e->d.head_dim, e->prop.multiProcessorCount);
+  }
   e->stats.sm_count = e->prop.multiProcessorCount; e->stats.cc_major = e->prop.major; e->stats.cc_minor = e->prop.minor;
   E_TRY(cudaStreamCreateWithFlags(&e->stream, cudaStreamNonBlocking));
   E_TRY(cudaEventCreate(&e->ev0));
@@ -539,6 +547,14 @@ static int create_impl(llmc_engine* e, const llmc_config& c) {
       E_TRY(cudaMemsetAsync(e->mega_trace, 0, nt * sizeof(unsigned long long), e->stream));
     }
     E_TRY(cudaMemsetAsync(e->mega_counters, 0, (size_t)d.kv_heads * sizeof(unsigned), e->stream));
+    if (e->use_ringb) {
+      const size_t G4 = (size_t)4 * e->prop.multiProcessorCount;
+      if (int rc = dalloc(e, &e->ringb_scratch, decode_ring_batch_scratch_floats(d.q_heads, D))) return rc;
+      if (int rc = dalloc(e, &e->ringb_part_val, G4)) return rc;
+      if (int rc = dalloc(e, &e->ringb_part_idx, G4)) return rc;
+      if (int rc = dalloc(e, &e->ringb_counters, (size_t)4 * d.kv_heads)) return rc;
+      E_TRY(cudaMemsetAsync(e->ringb_counters, 0, (size_t)4 * d.kv_heads * sizeof(unsigned), e->stream));
+    }
     if (e->use_flow) {
       e->flow_nwords = decode_flow_words(H, QD, KD, I, d.q_heads, d.kv_heads, D, e->prop.multiProcessorCount);
       if (int rc = dalloc(e, &e->flow_words, e->flow_nwords)) return rc;
@@ -564,6 +580,8 @@ static int create_impl(llmc_engine* e, const llmc_config& c) {
   E_TRY(cudaStreamSynchronize(e->stream));
   E_TRY(cudaGetLastError());
   stage("workspaces, sync");
+  if (init_trace)
+    fprintf(stderr, "[init dev %d] 2..4 sequences: %s\n", c.device, e->use_ringb ? "decode_ring_batch (persistent)" : "kernel graph per step");
   if (init_trace)
     fprintf(stderr, "[init dev %d] batch-1 decode path: %s\n", c.device,
             !e->use_mega ? "kernel graph" : e->use_flow ? "decode_flow (ring, tagged-word hand-overs)" : e->use_ring_mma ? "decode_ring_mma (ring, mma.sync slots)"
@@ -744,13 +762,38 @@ static int decode_group(llmc_engine* e, const int32_t* slots, int32_t nslots, in
   // context it will reach (the graph is keyed by it)
   const int nsplit = attn_decode_nsplit(max_len + nsteps);
   cudaGraphExec_t ge = nullptr;
-  if (e->use_graph && !(e->use_mega && nslots == 1)) {
+  static const bool ringb_b1 = getenv("LLMC_RING_BATCH_B1") != nullptr;   // experiment knob: batch 1 through the batched kernel
+  const bool ringb = e->use_ringb && nslots >= (ringb_b1 ? 1 : 2) && nslots <= 4 && decode_ring_batch_supported(nslots, d.hidden, d.qd(), d.kd(), d.inter, d.vocab, d.q_heads, d.kv_heads,
+                                                 d.head_dim, e->prop.multiProcessorCount);
+  if (e->use_graph && !(e->use_mega && nslots == 1) && !ringb) {
     int rc = get_graph(e, nslots, want_logits, nsplit, &ge);
     if (rc != LLMC_OK) return rc;
   }
-  const bool mega = e->use_mega && nslots == 1;
+  const bool mega = e->use_mega && nslots == 1 && !ringb;
   if (mega) ge = nullptr;
   E_TRY(cudaEventRecord(e->ev0, s));
+  if (ringb) {
+    MegaArgs m;
+    memset(&m, 0, sizeof(m));
+    m.layers = e->d_mega_layers; m.L = d.layers; m.H = d.hidden; m.QD = d.qd(); m.KD = d.kd(); m.I = d.inter;
+    m.V = d.vocab; m.q_heads = d.q_heads; m.kv_heads = d.kv_heads; m.head_dim = d.head_dim; m.eps = d.rms_eps;
+    m.emb = e->emb; m.lmhead = e->lmhead; m.gf = e->gf; m.rope_cos = e->rope_cos; m.rope_sin = e->rope_sin;
+    m.block_table = e->d_block_table; m.bt_stride = e->pages_per_seq; m.page_size = e->page_size;
+    m.kv_fp32 = e->kv_fp32; m.seq_len = e->d_seq_len; m.next_token = e->d_next_token;
+    m.x = e->x; m.q = e->q; m.attn = e->attn; m.act = e->act; m.logits = want_logits ? e->logits : nullptr;
+    m.attn_scratch = e->ringb_scratch; m.max_tiles = e->mega_max_tiles; m.attn_counters = e->ringb_counters;
+    m.part_val = e->ringb_part_val; m.part_idx = e->ringb_part_idx; m.out_tokens = e->d_out_tokens; m.nsteps = nsteps;
+    m.out_stride = MAX_STEPS_PER_CALL; m.slots = e->d_slots; m.B = nslots;
+    m.barrier = e->mega_barrier;
+    {
+      const char* tpb = getenv("LLMC_MEGA_TILES_PER_BLOCK");
+      m.attn_tiles_per_block = tpb ? std::max(1, atoi(tpb)) : 4;
+    }
+    m.trace = (e->mega_trace && nsteps <= 64) ? e->mega_trace : nullptr;
+    E_TRY(cudaMemsetAsync(e->mega_barrier, 0, 4 * sizeof(unsigned), s));
+    E_TRY(launch_decode_ring_batch(m, e->prop.multiProcessorCount, s));
+    e->stats.kernel_launches += 1;
+  }
   if (mega) {
     MegaArgs m;
     memset(&m, 0, sizeof(m));
@@ -791,7 +834,7 @@ static int decode_group(llmc_engine* e, const int32_t* slots, int32_t nslots, in
     else E_TRY(launch_decode_mega(m, e->prop.multiProcessorCount, s));
     e->stats.kernel_launches += 1;
   }
-  for (int st = 0; st < nsteps && !mega; ++st) {
+  for (int st = 0; st < nsteps && !mega && !ringb; ++st) {
     if (ge) {
       E_TRY(cudaGraphLaunch(ge, s));
       e->stats.kernel_launches += nslots >= e->wide_min_batch ? (uint64_t)d.layers * 7 + 5 : (uint64_t)d.layers * 5 + 1;
@@ -808,7 +851,7 @@ static int decode_group(llmc_engine* e, const int32_t* slots, int32_t nslots, in
     E_TRY(cudaMemcpyAsync(logits, e->logits, (size_t)nslots * d.vocab * sizeof(float), cudaMemcpyDeviceToHost, s));
   E_TRY(cudaStreamSynchronize(s));
   E_TRY(cudaGetLastError());
-  if (mega && e->mega_trace && nsteps <= 64) {
+  if ((mega || ringb) && e->mega_trace && nsteps <= 64) {
     // debug trace: average per-phase time (barrier open -> next barrier open) and barrier wait of block 0
     const int nb = (5 * d.layers + 1) * nsteps;
     std::vector<unsigned long long> t((size_t)2 * nb + 16 + 5 * 256);
@@ -824,14 +867,20 @@ static int decode_group(llmc_engine* e, const int32_t* slots, int32_t nslots, in
       cnt[k]++;
     }
     for (int k = 0; k < 6; ++k)
-      if (cnt[k]) fprintf(stderr, "[%s trace] %-7s phase %.2f us (block 0 waited %.2f us at its barrier) x%d\n", e->use_flow ? "flow" : e->use_ring ? "ring" : "mega", names[k],
+      if (cnt[k]) fprintf(stderr, "[%s trace] %-7s phase %.2f us (block 0 waited %.2f us at its barrier) x%d\n", ringb ? "ring batch" : e->use_flow ? "flow" : e->use_ring ? "ring" : "mega", names[k],
                           phase[k] / cnt[k] / 1e3, wait[k] / cnt[k] / 1e3, cnt[k]);
-    if (e->use_flow) {
+    if (ringb) {
+      const unsigned long long* st = t.data() + (size_t)2 * nb;
+      fprintf(stderr, "[ring batch stats] block 0 warp 0, cycles: total %llu = wait-full %llu + activation loads %llu + slots %llu "
+                      "(%llu slots seen; K = 2048 phases only) + exchanges %llu + grid barriers %llu + rest\n",
+              st[4], st[0], st[1], st[2], st[5], st[6], st[3]);
+    }
+    if (mega && e->use_flow) {
       const unsigned long long* st = t.data() + (size_t)2 * nb;
       fprintf(stderr, "[flow stats] block 0 warp 0, cycles: total %llu = wait-full %llu + activation loads %llu + slots %llu "
                       "(%llu slots seen) + hand-overs (all-writer) %llu + rest\n", st[4], st[0], st[1], st[2], st[5], st[3]);
     }
-    if (e->use_ring && !e->use_flow) {
+    if (mega && e->use_ring && !e->use_flow) {
       const unsigned long long* st = t.data() + (size_t)2 * nb;
       if (nsteps > 1) {
         const int G = e->prop.multiProcessorCount;

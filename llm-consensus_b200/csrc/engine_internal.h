@@ -79,6 +79,11 @@ struct llmc_engine {
   int wide_min_batch = 2;  // batches >= this use the wide (GEMM) decode path (LLMC_WIDE_MIN_BATCH=9: GEMV kernels up to 8)
   bool use_ring = false;  // persistent batch-1 decode through the TMA shared-memory ring (decode_ring.cu)
   bool use_ring_mma = false;  // ... with the slot arithmetic on mma.sync (decode_ring_mma.cu)
+  bool use_ringb = false;  // 2..4 sequences: one persistent launch per decode call (decode_ring_batch.cu)
+  float* ringb_scratch = nullptr;   // split-attention records of 4 sequences
+  float* ringb_part_val = nullptr;  // [4][SMs] argmax candidates
+  int* ringb_part_idx = nullptr;
+  unsigned* ringb_counters = nullptr;   // [4][kv_heads], zero between launches
   bool use_flow = false;  // ... with tagged-word hand-overs instead of grid barriers (decode_flow.cu)
   unsigned long long* flow_words = nullptr;   // the tagged-word buffers of decode_flow.cu
   size_t flow_nwords = 0;

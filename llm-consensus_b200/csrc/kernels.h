@@ -129,6 +129,11 @@ struct MegaArgs {
   unsigned long long* tw;      // decode_flow_words() 8-byte words, zero before the first launch
   unsigned tag0;               // first tag of this launch (>= 1); the launch uses nsteps * (5 L + 1) consecutive tags
   int flow_poll_mode;          // 0: one lane per warp watches the first word, then the warp reads; 1: every thread polls
+  // decode_ring_batch.cu only: B = 2..4 sequences; x / q / attn / act are [B] rows, logits [B][V], part_val / part_idx
+  // [4][grid], attn_counters [4][kv_heads], attn_scratch decode_ring_batch_scratch_floats()
+  const int* slots;            // device [B]
+  int B;
+  int out_stride;              // out_tokens[seq * out_stride + step]
 };
 cudaError_t launch_decode_mega(const MegaArgs& a, int sm_count, cudaStream_t s);
 // ------------------------------------------------------------------ decode_ring.cu
@@ -139,6 +144,12 @@ cudaError_t launch_decode_ring(const MegaArgs& a, int sm_count, cudaStream_t s);
 // the ring kernel with the slot arithmetic on mma.sync (weights = B operand, activation = hi / mid / lo rows of A)
 bool decode_ring_mma_supported(int H, int QD, int KD, int I, int V, int q_heads, int kv_heads, int head_dim);
 cudaError_t launch_decode_ring_mma(const MegaArgs& a, int sm_count, cudaStream_t s);
+// ------------------------------------------------------------------ decode_ring_batch.cu
+// the mma.sync ring kernel for 2..4 sequences per launch (pairs of sequences as the B columns, hi + mid parts)
+bool decode_ring_batch_supported(int B, int H, int QD, int KD, int I, int V, int q_heads, int kv_heads, int head_dim,
+                                 int sm_count);
+size_t decode_ring_batch_scratch_floats(int q_heads, int head_dim);
+cudaError_t launch_decode_ring_batch(const MegaArgs& a, int sm_count, cudaStream_t s);
 // ------------------------------------------------------------------ decode_flow.cu
 // the ring kernel without grid barriers: every activation travels as an 8-byte (value, tag) word that its readers
 // poll, so a phase hand-over costs one store-to-load trip through L2 instead of fence + arrive + poll + reload

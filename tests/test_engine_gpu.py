@@ -520,6 +520,53 @@ def test_wide_decode_engine_flags(gpu, B, flags):
     e.close()
 
 
+@pytest.mark.parametrize("flags", [0, 4, 128])     # fp32 KV, bf16 KV, and the per-step kernel graph as the comparator
+@pytest.mark.parametrize("name,B", [("wide-1b", 2), ("wide-1b", 3), ("wide-1b", 4), ("wide-d128", 2), ("wide-d128", 4)])
+def test_ring_batch_decode(gpu, name, B, flags):
+    """2..4 sequences through the persistent batched ring kernel (decode_ring_batch.cu): sequences of different
+    lengths (one context long enough for several attention splits), two decode calls in a row (the second starts from
+    the state the first left on the device), every sequence against its own oracle run."""
+    V = DIMS[name]["vocab"]
+    e = gpu.Engine(dims=DIMS[name], seed=21, max_ctx=512, max_slots=4, prefill_impl=DEFAULT_IMPL, flags=flags)
+    o = ref.Oracle(name, seed=21, max_ctx=512)
+    rng = np.random.default_rng(B * 7 + flags)
+    lens = [330, 5, 97, 140][:B]
+    prompts = [rng.integers(0, V, n) for n in lens]
+    slots, firsts = [], []
+    for p in prompts:
+        s = e.seq_alloc()
+        slots.append(s)
+        firsts.append(e.prefill(s, p))
+    out1 = e.decode(slots, 5)
+    out2, lg = e.decode(slots, 4, want_logits=True)
+    out = [np.concatenate([out1[i], out2[i]]) for i in range(B)]
+    tol = TOL if not flags & 12 else 8e-2
+    worst, ties = check_batched(o, prompts, firsts, out, lg, 9, tol=tol)
+    assert [e.seq_len(s) for s in slots] == [n + 9 for n in lens]
+    print("%s, %d sequences, flags %d: worst last-step logit err %.3e (%d on their own path after a tie)" % (name, B, flags, worst, ties))
+    e.close()
+
+
+def test_ring_batch_decode_full_size_1b(gpu):
+    """The batched ring kernel at the full Llama-3.2-1B shape: 4 sequences, a long and three short contexts, against the
+    oracle; then the same slots continue as two pairs (batch 2) and must produce the tokens the oracle continues with."""
+    n_new = 6
+    o = ref.Oracle("llama-1b", seed=0, max_ctx=256)
+    e = gpu.Engine(shape=gpu.SHAPE_LLAMA_1B, seed=0, max_ctx=256, max_slots=4, prefill_impl=DEFAULT_IMPL)
+    rng = np.random.default_rng(78)
+    prompts = [rng.integers(0, 128256, n) for n in (150, 7, 40, 66)]
+    slots, firsts = [], []
+    for p in prompts:
+        s = e.seq_alloc()
+        slots.append(s)
+        firsts.append(e.prefill(s, p))
+    out, lg = e.decode(slots, n_new, want_logits=True)
+    worst, ties = check_batched(o, prompts, firsts, out, lg, n_new)
+    print("ring batch, 1B shape, 4 sequences: worst last-step logit err %.3e (%d on their own path after a tie)" % (worst, ties))
+    assert worst <= TOL
+    e.close()
+
+
 def test_wide_decode_long_context_two_attention_blocks(gpu):
     """Wide path with contexts past 2 048 tokens: the decode attention then runs two blocks per (sequence, kv head);
     the one that owns the last tile applies RoPE to the new K row and appends K/V itself."""
