@@ -16,6 +16,8 @@
 // split-K (gridDim.z) as in gemm_tcgen05.cu for the matrices with few row tiles (QKV, O, down).
 //
 // No counterpart in the reference (/root/reference/internal/provider/provider.go:13-21 is the boundary).
+#include <cstdlib>
+
 #include "common.cuh"
 #include "kernels.h"
 #include "tc_common.cuh"
@@ -38,7 +40,10 @@ __device__ __forceinline__ void tc_ld16(uint32_t taddr, uint32_t (&r)[16]) {
       : "r"(taddr));
 }
 
-template <int NB, bool SPLIT>
+// HALF: half the shared-memory budget per block, so that two blocks fit on an SM -- under programmatic dependent launch
+// the NEXT kernel's blocks can then become resident and request their first weight tiles while this kernel's blocks are
+// still in their epilogue
+template <int NB, bool SPLIT, bool HALF>
 struct DCfg {
   static constexpr int W_BYTES = DM * DK * 2;                 // 16 KB
   static constexpr int A_BYTES = NB * DK * 2;                 // NB * 128 B
@@ -46,17 +51,18 @@ struct DCfg {
   static constexpr int A_ALLOC = (A_BYTES + 1023) / 1024 * 1024;   // swizzled tiles start on 1024 B
   static constexpr int STAGE_BYTES = W_BYTES + A_TILES * A_ALLOC;
   static constexpr int TX_BYTES = W_BYTES + A_TILES * A_BYTES;
-  static constexpr int STAGES = (192 * 1024 / STAGE_BYTES) > 10 ? 10 : (192 * 1024 / STAGE_BYTES);
+  static constexpr int BUDGET = HALF ? 100 * 1024 : 192 * 1024;
+  static constexpr int STAGES = (BUDGET / STAGE_BYTES) > 10 ? 10 : (BUDGET / STAGE_BYTES);
   static constexpr int SMEM = STAGES * STAGE_BYTES + 1024 /*alignment slack*/ + 256 /*barriers*/;
   static constexpr int TMEM_COLS = NB < 32 ? 32 : NB;
 };
 
-template <int NB, int EPI, bool SPLIT>
+template <int NB, int EPI, bool SPLIT, bool HALF>
 __global__ void __launch_bounds__(DTHREADS, 1)
     gemm_decode_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmAlo,
                        const __grid_constant__ CUtensorMap tmW, void* __restrict__ out, void* __restrict__ out_lo,
                        int B, int N, int K) {
-  using C = DCfg<NB, SPLIT>;
+  using C = DCfg<NB, SPLIT, HALF>;
   extern __shared__ unsigned char smem_raw[];
   const uint32_t raw = smem_u32(smem_raw);
   const uint32_t base = (raw + 1023u) & ~1023u;
@@ -216,25 +222,25 @@ __global__ void __launch_bounds__(DTHREADS, 1)
   }
 }
 
-int pick_ksplit(int tiles, int kblocks) {
+int pick_ksplit(int tiles, int kblocks, int max_blocks) {
   int s = 1;
-  while (s < 32 && tiles * (s * 2) <= 160 && kblocks % (s * 2) == 0 && kblocks / (s * 2) >= 4) s *= 2;
+  while (s < 32 && tiles * (s * 2) <= max_blocks && kblocks % (s * 2) == 0 && kblocks / (s * 2) >= 4) s *= 2;
   return s;
 }
 
-template <int NB, int EPI, bool SPLIT>
-cudaError_t launch_nb(const uint16_t* A, const uint16_t* Alo, const uint16_t* W, void* out, void* out_lo, int B, int N,
-                      int K, cudaStream_t s, bool pdl) {
-  using C = DCfg<NB, SPLIT>;
+template <int NB, int EPI, bool SPLIT, bool HALF>
+cudaError_t launch_nbh(const uint16_t* A, const uint16_t* Alo, const uint16_t* W, void* out, void* out_lo, int B, int N,
+                       int K, cudaStream_t s, bool pdl) {
+  using C = DCfg<NB, SPLIT, HALF>;
   CUtensorMap ma, ml, mw;
   if (!make_map(&ma, A, (uint64_t)B, (uint64_t)K, NB) || !make_map(&mw, W, (uint64_t)N, (uint64_t)K, DM) ||
       !make_map(&ml, SPLIT ? Alo : A, (uint64_t)B, (uint64_t)K, NB))
     return cudaErrorInvalidValue;
-  auto kern = gemm_decode_kernel<NB, EPI, SPLIT>;
+  auto kern = gemm_decode_kernel<NB, EPI, SPLIT, HALF>;
   cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM);
   if (e != cudaSuccess) return e;
   const int tiles = N / DM;
-  const int ks = (EPI == GEMM_SWIGLU_BF16) ? 1 : pick_ksplit(tiles, K / DK);
+  const int ks = (EPI == GEMM_SWIGLU_BF16) ? 1 : pick_ksplit(tiles, K / DK, HALF ? 300 : 160);
   if (ks > 1 && EPI == GEMM_STORE_F32) {
     e = cudaMemsetAsync(out, 0, (size_t)B * N * sizeof(float), s);
     if (e != cudaSuccess) return e;
@@ -242,6 +248,18 @@ cudaError_t launch_nb(const uint16_t* A, const uint16_t* Alo, const uint16_t* W,
   // (a memset node in front of the kernel is an ordinary dependency: no programmatic edge then)
   return launch_maybe_pdl(kern, dim3(tiles, 1, ks), dim3(DTHREADS), (size_t)C::SMEM, s,
                           pdl && !(ks > 1 && EPI == GEMM_STORE_F32), ma, ml, mw, out, out_lo, B, N, K);
+}
+
+template <int NB, int EPI, bool SPLIT>
+cudaError_t launch_nb(const uint16_t* A, const uint16_t* Alo, const uint16_t* W, void* out, void* out_lo, int B, int N,
+                      int K, cudaStream_t s, bool pdl) {
+  // batch <= 32: two blocks per SM (measured at the 1B shape: batch 8 1.044 -> 0.955 ms per step, 16: 1.086 -> 0.983,
+  // 32: 1.386 -> 1.322); LLMC_GEMM_HALF=0 restores one block per SM with the whole shared memory as its ring
+  static const bool half = !(getenv("LLMC_GEMM_HALF") && atoi(getenv("LLMC_GEMM_HALF")) == 0);
+  if constexpr (NB <= 32) {
+    if (half) return launch_nbh<NB, EPI, SPLIT, true>(A, Alo, W, out, out_lo, B, N, K, s, pdl);
+  }
+  return launch_nbh<NB, EPI, SPLIT, false>(A, Alo, W, out, out_lo, B, N, K, s, pdl);
 }
 
 template <int EPI, bool SPLIT>
