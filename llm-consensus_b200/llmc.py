@@ -14,6 +14,7 @@ LIB_PATH = os.path.join(_HERE, "lib", "libllmc.so")
 
 SHAPE_CUSTOM, SHAPE_LLAMA_1B, SHAPE_LLAMA_8B = 0, 1, 2
 FLAG_NO_GRAPH, FLAG_NO_PDL, FLAG_KV_BF16, FLAG_PREFILL_BF16 = 1, 2, 4, 8
+FLAG_NO_MEGAKERNEL, FLAG_NO_RING, FLAG_RING_FLOW, FLAG_NO_RING_BATCH, FLAG_RING_MMA = 16, 32, 64, 128, 256
 OK, ERR_INVALID, ERR_CUDA, ERR_OOM, ERR_STATE, ERR_LIMIT = 0, -1, -2, -3, -4, -5
 
 # every symbol the headers declare (checked by tests/test_abi_symbols.py)
