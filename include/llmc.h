@@ -111,6 +111,13 @@ void llmc_engine_destroy(llmc_engine* e);
 /* Sequence slots: one per in-flight QueryStream call. */
 int llmc_seq_alloc(llmc_engine* e, int32_t* slot);
 int llmc_seq_free(llmc_engine* e, int32_t slot);
+/* New slot holding the first n_tokens (1..llmc_seq_len(src)) cached tokens of slot src: full KV pages are shared
+ * read-only (reference-counted; both sequences only ever append behind them), the page holding the last
+ * n_tokens % page_size positions is copied.  n_tokens == llmc_seq_len(src) also copies the pending token, so the fork
+ * decodes exactly what src would.  This is how the provider serves what the reference sends it repeatedly: the same
+ * prompt once per duplicate --models entry (/root/reference/internal/runner/runner.go:62-95 starts one goroutine per
+ * entry, no dedupe) and the judge prompt's fixed head (/root/reference/internal/consensus/judge.go:12-19, 96-99). */
+int llmc_seq_fork(llmc_engine* e, int32_t src, int32_t n_tokens, int32_t* new_slot);
 /* tokens currently held in the slot's KV cache */
 int llmc_seq_len(llmc_engine* e, int32_t slot, int32_t* len);
 

@@ -157,6 +157,7 @@ int ensure_pages(llmc_engine* e, int slot, int need_tokens) {
   for (int i = have; i < need; ++i) {
     row[i] = e->free_pages.back();
     e->free_pages.pop_back();
+    e->page_ref[row[i]] = 1;
   }
   E_TRY(cudaMemcpyAsync(e->d_block_table + (size_t)slot * e->pages_per_seq + have, row + have,
                         (size_t)(need - have) * sizeof(int), cudaMemcpyHostToDevice, e->stream));
@@ -467,6 +468,7 @@ static int create_impl(llmc_engine* e, const llmc_config& c) {
   e->h_block_table.assign((size_t)e->max_slots * e->pages_per_seq, 0);
   for (int p = e->num_pages - 1; p >= 0; --p) e->free_pages.push_back(p);
   e->slot_npages.assign(e->max_slots, 0);
+  e->page_ref.assign(e->num_pages, 0);
   e->slot_used.assign(e->max_slots, 0);
   e->h_seq_len.assign(e->max_slots, 0);
   if (int rc = dalloc(e, &e->d_seq_len, e->max_slots)) return rc;
@@ -645,13 +647,69 @@ int llmc_seq_free(llmc_engine* e, int32_t slot) {
   E_TRY(cudaSetDevice(e->device));
   E_TRY(cudaStreamSynchronize(e->stream));
   int* row = &e->h_block_table[(size_t)slot * e->pages_per_seq];
-  for (int i = 0; i < e->slot_npages[slot]; ++i) e->free_pages.push_back(row[i]);
+  for (int i = 0; i < e->slot_npages[slot]; ++i)
+    if (--e->page_ref[row[i]] == 0) e->free_pages.push_back(row[i]);   // pages shared with a fork live on
   e->slot_npages[slot] = 0;
   e->slot_used[slot] = 0;
   e->h_seq_len[slot] = 0;
   int zero = 0;
   E_TRY(cudaMemcpyAsync(e->d_seq_len + slot, &zero, sizeof(int), cudaMemcpyHostToDevice, e->stream));
   E_TRY(cudaStreamSynchronize(e->stream));
+  return LLMC_OK;
+}
+
+int llmc_seq_fork(llmc_engine* e, int32_t src, int32_t n_tokens, int32_t* new_slot) {
+  if (!e || !new_slot) return LLMC_ERR_INVALID;
+  std::lock_guard<std::mutex> lk(e->mu);
+  if (int rc = check_slot(e, src)) return rc;
+  if (n_tokens < 1 || n_tokens > e->h_seq_len[src])
+    return fail(e, LLMC_ERR_INVALID, "llmc_seq_fork: n_tokens must be in [1, " + std::to_string(e->h_seq_len[src]) + "]");
+  int dst = -1;
+  for (int s = 0; s < e->max_slots; ++s)
+    if (!e->slot_used[s]) { dst = s; break; }
+  if (dst < 0) return fail(e, LLMC_ERR_LIMIT, "all " + std::to_string(e->max_slots) + " sequence slots are in use");
+  const int full = n_tokens / e->page_size, rem = n_tokens % e->page_size;
+  if (rem && e->free_pages.empty()) return fail(e, LLMC_ERR_OOM, "KV page pool exhausted");
+  E_TRY(cudaSetDevice(e->device));
+  cudaStream_t s = e->stream;
+  const int* srow = &e->h_block_table[(size_t)src * e->pages_per_seq];
+  int* drow = &e->h_block_table[(size_t)dst * e->pages_per_seq];
+  // full pages are never written again (both sequences append behind them): shared.  The page that holds the last
+  // n_tokens % page_size positions is copied, all layers, K and V: one strided copy per pool.
+  for (int i = 0; i < full; ++i) {
+    drow[i] = srow[i];
+    ++e->page_ref[srow[i]];
+  }
+  int npages = full;
+  if (rem) {
+    const int pg = e->free_pages.back();
+    e->free_pages.pop_back();
+    e->page_ref[pg] = 1;
+    drow[full] = pg;
+    npages = full + 1;
+    const size_t page_bytes = (size_t)e->d.kd() * e->page_size * e->kv_elem;
+    const size_t pitch = e->kv_layer_stride * e->kv_elem;
+    for (unsigned char* pool : {e->kpool, e->vpool}) {
+      unsigned char* to = pool + (size_t)pg * page_bytes;
+      const unsigned char* from = pool + (size_t)srow[full] * page_bytes;
+      if (pitch <= e->prop.memPitch) {
+        E_TRY(cudaMemcpy2DAsync(to, pitch, from, pitch, page_bytes, e->d.layers, cudaMemcpyDeviceToDevice, s));
+      } else {   // very large pools: the 2-D copy's pitch limit
+        for (int l = 0; l < e->d.layers; ++l)
+          E_TRY(cudaMemcpyAsync(to + (size_t)l * pitch, from + (size_t)l * pitch, page_bytes, cudaMemcpyDeviceToDevice, s));
+      }
+    }
+  }
+  e->slot_used[dst] = 1;
+  e->slot_npages[dst] = npages;
+  e->h_seq_len[dst] = n_tokens;
+  E_TRY(cudaMemcpyAsync(e->d_block_table + (size_t)dst * e->pages_per_seq, drow, (size_t)npages * sizeof(int),
+                        cudaMemcpyHostToDevice, s));
+  E_TRY(cudaMemcpyAsync(e->d_seq_len + dst, &e->h_seq_len[dst], sizeof(int), cudaMemcpyHostToDevice, s));
+  if (n_tokens == e->h_seq_len[src])   // a clone at the source's end also inherits its pending token
+    E_TRY(cudaMemcpyAsync(e->d_next_token + dst, e->d_next_token + src, sizeof(int), cudaMemcpyDeviceToDevice, s));
+  E_TRY(cudaStreamSynchronize(s));
+  *new_slot = dst;
   return LLMC_OK;
 }
 

@@ -57,6 +57,7 @@ struct llmc_engine {
   std::vector<int> free_pages;
   std::vector<int> slot_npages;
   std::vector<char> slot_used;
+  std::vector<int> page_ref;   // sequences holding each KV page (llmc_seq_fork shares full pages read-only)
   std::vector<int> h_seq_len;
   int *d_seq_len = nullptr, *d_next_token = nullptr;
   float *rope_cos = nullptr, *rope_sin = nullptr;

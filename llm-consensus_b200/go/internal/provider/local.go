@@ -13,6 +13,7 @@ import (
 	"fmt"
 	"runtime"
 	"sync"
+	"sync/atomic"
 	"time"
 	"unsafe"
 )
@@ -45,7 +46,15 @@ type Local struct {
 	slots chan struct{} // counting semaphore over the engine's sequence slots
 	join  chan *job
 	once  sync.Once
+
+	admitting atomic.Int32 // callers inside prefill(): the scheduler pauses for them between chunks
+
+	cacheMu   sync.Mutex // the prompt cache and the prefill that refreshes it
+	cacheSlot C.int32_t  // slot holding the KV cache of the last prompt prefilled here, -1 = none
+	cacheIDs  []int32
 }
+
+const minPrefix = 32 // shorter common prefixes are not worth a fork
 
 func NewLocal(cfg LocalConfig) (*Local, error) {
 	if cfg.MaxSlots <= 0 {
@@ -53,7 +62,7 @@ func NewLocal(cfg LocalConfig) (*Local, error) {
 	}
 	var c C.llmc_config
 	c.device, c.shape, c.seed = C.int32_t(cfg.Device), C.int32_t(cfg.Shape), C.uint64_t(cfg.Seed)
-	c.max_slots, c.max_ctx = C.int32_t(cfg.MaxSlots), C.int32_t(cfg.MaxCtx)
+	c.max_slots, c.max_ctx = C.int32_t(cfg.MaxSlots+1), C.int32_t(cfg.MaxCtx) // + the slot that holds the cached prompt
 	if cfg.WeightsPath != "" {
 		p := C.CString(cfg.WeightsPath)
 		defer C.free(unsafe.Pointer(p))
@@ -63,7 +72,7 @@ func NewLocal(cfg LocalConfig) (*Local, error) {
 	if rc := C.llmc_engine_create(&c, &e); rc != C.LLMC_OK {
 		return nil, fmt.Errorf("local provider: %s", C.GoString(C.llmc_last_error(nil)))
 	}
-	l := &Local{e: e, cfg: cfg, vocab: 128256, slots: make(chan struct{}, cfg.MaxSlots), join: make(chan *job, cfg.MaxSlots)}
+	l := &Local{e: e, cfg: cfg, vocab: 128256, slots: make(chan struct{}, cfg.MaxSlots), join: make(chan *job, cfg.MaxSlots), cacheSlot: -1}
 	for i := 0; i < cfg.MaxSlots; i++ {
 		l.slots <- struct{}{}
 	}
@@ -98,15 +107,16 @@ func (l *Local) QueryStream(ctx context.Context, req Request, cb StreamCallback)
 		return Response{}, ctx.Err()
 	}
 	defer func() { l.slots <- struct{}{} }()
-	var slot C.int32_t
-	if C.llmc_seq_alloc(l.e, &slot) != C.LLMC_OK {
-		return Response{}, l.err("allocating a sequence slot")
+	// The scheduler holds the engine for a whole chunk per llmc_decode call and would take it again at once; while a
+	// caller is being admitted it pauses between chunks, so the newcomer joins at the next chunk boundary.
+	l.admitting.Add(1)
+	slot, first, err := l.prefill(ids)
+	l.admitting.Add(-1)
+	if slot >= 0 {
+		defer C.llmc_seq_free(l.e, slot)
 	}
-	defer C.llmc_seq_free(l.e, slot)
-
-	var first C.int32_t
-	if C.llmc_prefill(l.e, slot, (*C.int32_t)(unsafe.Pointer(&ids[0])), C.int32_t(len(ids)), &first, nil) != C.LLMC_OK {
-		return Response{}, l.err("prefill")
+	if err != nil {
+		return Response{}, err
 	}
 	content, stopped := "", false
 	emit := func(t []int32) {
@@ -160,6 +170,54 @@ func (l *Local) QueryStream(ctx context.Context, req Request, cb StreamCallback)
 	return Response{Model: req.Model, Content: content, Provider: "local", Latency: time.Since(start)}, nil
 }
 
+// prefill puts the prompt into a fresh slot.  The instance keeps the KV cache of the LAST prompt it prefilled in a
+// slot of its own (llmc_seq_fork: full pages shared, the tail page copied).  The runner sends the same prompt once
+// per duplicate --models entry (runner.go:62-95) and every judge prompt starts with the template's fixed head
+// (judge.go:12-19), so an identical prompt is a clone of the cached sequence, pending token included (no prefill,
+// bit-identical answer), and a prompt sharing >= minPrefix leading tokens forks the prefix and prefills the rest.
+func (l *Local) prefill(ids []int32) (C.int32_t, C.int32_t, error) {
+	l.cacheMu.Lock()
+	defer l.cacheMu.Unlock()
+	n, common := len(ids), 0
+	if l.cacheSlot >= 0 {
+		for common < n && common < len(l.cacheIDs) && ids[common] == l.cacheIDs[common] {
+			common++
+		}
+	}
+	slot, first := C.int32_t(-1), C.int32_t(-1)
+	if l.cacheSlot >= 0 && common == n && n == len(l.cacheIDs) {
+		if C.llmc_seq_fork(l.e, l.cacheSlot, C.int32_t(n), &slot) != C.LLMC_OK {
+			return -1, -1, l.err("cloning the cached prompt")
+		}
+		if C.llmc_seq_get_next_token(l.e, slot, &first) != C.LLMC_OK {
+			return slot, -1, l.err("reading the cached prompt's first token")
+		}
+		return slot, first, nil
+	}
+	have := 0
+	if l.cacheSlot >= 0 && common >= minPrefix {
+		have = min(common, n-1) // at least one token goes through the model: its logits pick the first answer token
+		if C.llmc_seq_fork(l.e, l.cacheSlot, C.int32_t(have), &slot) != C.LLMC_OK {
+			return -1, -1, l.err("forking the cached prefix")
+		}
+	} else if C.llmc_seq_alloc(l.e, &slot) != C.LLMC_OK {
+		return -1, -1, l.err("allocating a sequence slot")
+	}
+	if C.llmc_prefill(l.e, slot, (*C.int32_t)(unsafe.Pointer(&ids[have])), C.int32_t(n-have), &first, nil) != C.LLMC_OK {
+		return slot, -1, l.err("prefill")
+	}
+	if l.cacheSlot >= 0 { // this prompt becomes the cached one
+		C.llmc_seq_free(l.e, l.cacheSlot)
+	}
+	l.cacheSlot = -1
+	if C.llmc_seq_fork(l.e, slot, C.int32_t(n), &l.cacheSlot) == C.LLMC_OK {
+		l.cacheIDs = append(l.cacheIDs[:0], ids...)
+	} else {
+		l.cacheSlot = -1 // no room: carry on without a cache
+	}
+	return slot, first, nil
+}
+
 // schedule runs on its own goroutine for the life of the provider.
 func (l *Local) schedule(chunk int) {
 	runtime.LockOSThread()
@@ -171,6 +229,9 @@ func (l *Local) schedule(chunk int) {
 				return
 			}
 			live = append(live, j)
+		}
+		for l.admitting.Load() > 0 { // a caller is prefilling: let it have the engine
+			time.Sleep(50 * time.Microsecond)
 		}
 		for more := true; more; { // whoever else has finished its prefill joins at this chunk boundary
 			select {

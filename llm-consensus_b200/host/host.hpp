@@ -176,8 +176,12 @@ struct LocalConfig {
   int flags = 0;
   int max_slots = 4;         // sequences that can be in flight on this instance; further callers wait for a slot
   std::vector<int32_t> stop_ids;  // generation ends before the first of these ids (e.g. 128001 / 128009 for Llama-3)
+  bool prompt_cache = true;  // keep the last prompt's KV: an identical prompt is cloned, a shared prefix (>= 32 tokens) is not prefilled again
 };
 // provider.NewLocal: builds an engine through the C ABI (include/llmc.h); Provider tag "local"
 Error NewLocal(const LocalConfig& cfg, std::shared_ptr<Provider>* out);
+// forget every local instance's cached prompt (the CLI's measurement loop calls it between passes, so that a pass
+// never starts with the previous pass's prompts already in the KV cache)
+void DropPromptCaches();
 
 }  // namespace host

@@ -6,6 +6,7 @@
 #include <algorithm>
 #include <chrono>
 #include <condition_variable>
+#include <cstdlib>
 #include <deque>
 #include <mutex>
 #include <thread>
@@ -23,11 +24,22 @@ namespace {
 // that advances ALL live sequences together, one llmc_decode(slots[], n, k) per chunk -- one pass over the
 // weights per step for the whole group (the wide decode path) instead of one pass per caller.  Chunks go back
 // to the callers, which emit them through their own callback on their own thread, as provider.go:10 requires.
+class Local;
+std::mutex g_locals_mu;
+std::vector<Local*> g_locals;   // live instances, for DropPromptCaches()
+
 class Local : public Provider {
  public:
   Local(llmc_engine* e, const LocalConfig& cfg, int vocab, int max_slots)
-      : e_(e), cfg_(cfg), vocab_(vocab), free_slots_(max_slots) {}
+      : e_(e), cfg_(cfg), vocab_(vocab), free_slots_(max_slots) {
+    std::lock_guard<std::mutex> lk(g_locals_mu);
+    g_locals.push_back(this);
+  }
   ~Local() override {
+    {
+      std::lock_guard<std::mutex> lk(g_locals_mu);
+      g_locals.erase(std::remove(g_locals.begin(), g_locals.end(), this), g_locals.end());
+    }
     {
       std::lock_guard<std::mutex> lk(mu_);
       stop_ = true;
@@ -39,6 +51,13 @@ class Local : public Provider {
 
   Error Query(const Context& ctx, const Request& req, Response* out) override {
     return QueryStream(ctx, req, nullptr, out);  // never called by the CLI path (runner.go:92, judge.go:96)
+  }
+
+  void drop_prompt_cache() {
+    std::lock_guard<std::mutex> lk(cache_mu_);
+    if (cache_slot_ >= 0) llmc_seq_free(e_, cache_slot_);
+    cache_slot_ = -1;
+    cache_ids_.clear();
   }
 
   Error QueryStream(const Context& ctx, const Request& req, const StreamCallback& cb, Response* out) override {
@@ -72,7 +91,6 @@ class Local : public Provider {
       Job* j;
       ~Release() { p->release(j); }
     } guard{this, &job};
-    if (llmc_seq_alloc(e_, &job.slot) != LLMC_OK) return fail("allocating a sequence slot");
     std::string content;
     bool stopped = false;
     auto emit = [&](const int32_t* t, size_t n) {
@@ -87,7 +105,22 @@ class Local : public Provider {
       if (cb) cb(chunk);
     };
     int32_t first = -1;
-    if (llmc_prefill(e_, job.slot, ids.data(), (int32_t)ids.size(), &first, nullptr) != LLMC_OK) return fail("prefill");
+    {
+      // The scheduler thread holds the engine for a whole chunk per llmc_decode call and would take it again at once: a
+      // caller waiting to prefill could starve behind it until the running sequences finish.  While anyone is being
+      // admitted the scheduler pauses between chunks, so newcomers join at the next chunk boundary.
+      {
+        std::lock_guard<std::mutex> lk(mu_);
+        ++admitting_;
+      }
+      Error err = prefill(ids, &job.slot, &first);
+      {
+        std::lock_guard<std::mutex> lk(mu_);
+        --admitting_;
+      }
+      sched_cv_.notify_all();
+      if (err) return err;
+    }
     emit(&first, 1);
     job.left = cfg_.max_new_tokens - 1;
     if (job.left > 0 && !stopped) {
@@ -133,6 +166,46 @@ class Local : public Provider {
     std::condition_variable cv;
   };
 
+  // The prompt into a fresh slot.  The instance keeps the KV cache of the LAST prompt it prefilled in a slot of its own
+  // (llmc_seq_fork: full pages shared, the tail page copied).  The reference sends the same prompt once per duplicate
+  // --models entry (runner.go:62-95) and every judge prompt starts with the template's fixed head (judge.go:12-19), so:
+  //   * an identical prompt is a clone of the cached sequence, pending token included -- no prefill, and the answer is
+  //     bit-identical to the first caller's;
+  //   * a prompt that shares >= kMinPrefix leading tokens forks the prefix and prefills only the rest.
+  // One prefill at a time per instance (the engine serialises them anyway).
+  static constexpr int kMinPrefix = 32;
+  Error prefill(const std::vector<int32_t>& ids, int32_t* slot, int32_t* first) {
+    std::lock_guard<std::mutex> lk(cache_mu_);
+    const int n = (int)ids.size();
+    int common = 0;
+    if (cache_slot_ >= 0) {
+      const int m = std::min(n, (int)cache_ids_.size());
+      while (common < m && ids[common] == cache_ids_[common]) ++common;
+    }
+    if (cache_slot_ >= 0 && common == n && n == (int)cache_ids_.size()) {
+      if (llmc_seq_fork(e_, cache_slot_, n, slot) != LLMC_OK) return fail("cloning the cached prompt");
+      if (llmc_seq_get_next_token(e_, *slot, first) != LLMC_OK) return fail("reading the cached prompt's first token");
+      ++cache_hits_;
+      return Error::Nil();
+    }
+    int have = 0;
+    if (cache_slot_ >= 0 && common >= kMinPrefix) {
+      have = std::min(common, n - 1);   // at least one token goes through the model: its logits pick the first answer token
+      if (llmc_seq_fork(e_, cache_slot_, have, slot) != LLMC_OK) return fail("forking the cached prefix");
+      ++cache_hits_;
+    } else if (llmc_seq_alloc(e_, slot) != LLMC_OK) {
+      return fail("allocating a sequence slot");
+    }
+    if (llmc_prefill(e_, *slot, ids.data() + have, n - have, first, nullptr) != LLMC_OK) return fail("prefill");
+    if (cfg_.prompt_cache) {   // this prompt becomes the cached one
+      if (cache_slot_ >= 0) llmc_seq_free(e_, cache_slot_);
+      cache_slot_ = -1;
+      if (llmc_seq_fork(e_, *slot, n, &cache_slot_) == LLMC_OK) cache_ids_ = ids;
+      else cache_slot_ = -1;   // (no room: carry on without a cache)
+    }
+    return Error::Nil();
+  }
+
   static int64_t since(std::chrono::steady_clock::time_point t0) {
     return std::chrono::duration_cast<std::chrono::nanoseconds>(std::chrono::steady_clock::now() - t0).count();
   }
@@ -162,6 +235,7 @@ class Local : public Provider {
     while (true) {
       sched_cv_.wait(lk, [&] {
         if (stop_) return true;
+        if (admitting_ > 0) return false;
         for (Job* j : jobs_)
           if (j->left > 0) return true;
         return false;
@@ -206,13 +280,25 @@ class Local : public Provider {
   std::condition_variable sched_cv_, slot_cv_;
   std::vector<Job*> jobs_;
   int free_slots_;
+  int admitting_ = 0;                 // callers inside prefill(): the scheduler waits for them between chunks
   bool stop_ = false;
   std::thread sched_;
+  std::mutex cache_mu_;               // the prompt cache and the prefill that refreshes it
+  int32_t cache_slot_ = -1;
+  std::vector<int32_t> cache_ids_;
+  int64_t cache_hits_ = 0;
 };
 
 }  // namespace
 
-Error NewLocal(const LocalConfig& cfg, std::shared_ptr<Provider>* out) {
+void DropPromptCaches() {
+  std::lock_guard<std::mutex> lk(g_locals_mu);
+  for (Local* l : g_locals) l->drop_prompt_cache();
+}
+
+Error NewLocal(const LocalConfig& cfg_in, std::shared_ptr<Provider>* out) {
+  LocalConfig cfg = cfg_in;
+  if (const char* pc = getenv("LLMC_PROMPT_CACHE")) cfg.prompt_cache = atoi(pc) != 0;   // A/B switch for the tests
   llmc_config c{};
   c.device = cfg.device;
   c.shape = cfg.shape;
@@ -221,7 +307,7 @@ Error NewLocal(const LocalConfig& cfg, std::shared_ptr<Provider>* out) {
   c.seed = cfg.seed;
   c.weights_path = cfg.weights_path.empty() ? nullptr : cfg.weights_path.c_str();
   const int max_slots = std::max(1, std::min(cfg.max_slots, 128));
-  c.max_slots = max_slots;
+  c.max_slots = max_slots + (cfg.prompt_cache ? 1 : 0);   // + the slot that holds the cached prompt
   c.max_ctx = cfg.max_ctx;
   c.flags = cfg.flags;
   llmc_engine* e = nullptr;

@@ -321,6 +321,7 @@ Error run(int argc, char** argv) {
   RunResult result;
   std::string consensus;
   for (int pass = 0; pass < repeat; ++pass) {
+    if (pass > 0) DropPromptCaches();   // every pass starts like a fresh process: nothing of the last one is reused
     result = RunResult();
     consensus.clear();
     const auto t0 = clk::now();

@@ -20,7 +20,7 @@ OK, ERR_INVALID, ERR_CUDA, ERR_OOM, ERR_STATE, ERR_LIMIT = 0, -1, -2, -3, -4, -5
 # every symbol the headers declare (checked by tests/test_abi_symbols.py)
 ENGINE_SYMBOLS = [
     "llmc_device_count", "llmc_engine_create", "llmc_engine_destroy", "llmc_seq_alloc", "llmc_seq_free",
-    "llmc_seq_len", "llmc_prefill", "llmc_decode", "llmc_seq_set_next_token", "llmc_seq_get_next_token",
+    "llmc_seq_len", "llmc_seq_fork", "llmc_prefill", "llmc_decode", "llmc_seq_set_next_token", "llmc_seq_get_next_token",
     "llmc_engine_stats", "llmc_last_error", "llmc_version",
 ]
 OPS_SYMBOLS = [
@@ -71,6 +71,7 @@ def lib():
         l.llmc_seq_alloc.argtypes = [vp, C.POINTER(i32)]
         l.llmc_seq_free.argtypes = [vp, i32]
         l.llmc_seq_len.argtypes = [vp, i32, C.POINTER(i32)]
+        l.llmc_seq_fork.argtypes = [vp, i32, i32, C.POINTER(i32)]
         l.llmc_prefill.argtypes = [vp, i32, vp, i32, C.POINTER(i32), f32p]
         l.llmc_decode.argtypes = [vp, vp, i32, i32, vp, f32p]
         l.llmc_seq_set_next_token.argtypes = [vp, i32, i32]
@@ -167,6 +168,13 @@ class Engine:
         lg = np.empty(self.vocab, np.float32) if want_logits else None
         self._check(lib().llmc_prefill(self.h, slot, t.ctypes.data, len(t), C.byref(nxt), _ptr(lg)))
         return (nxt.value, lg) if want_logits else nxt.value
+
+    def seq_fork(self, src, n_tokens=None):
+        """New slot holding the first n_tokens (default: all) cached tokens of slot src (include/llmc.h: llmc_seq_fork)."""
+        s = C.c_int32(-1)
+        n = self.seq_len(src) if n_tokens is None else int(n_tokens)
+        self._check(lib().llmc_seq_fork(self.h, int(src), n, C.byref(s)))
+        return s.value
 
     def decode(self, slots, nsteps, want_logits=False):
         s = np.ascontiguousarray(slots, np.int32)

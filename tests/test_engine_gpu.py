@@ -316,6 +316,64 @@ def test_slots_are_independent_and_reusable(gpu):
     e.close()
 
 
+@pytest.mark.parametrize("flags", [0, 4])   # fp32 and bf16 KV pages
+def test_seq_fork_clone_prefix_and_page_sharing(gpu, flags):
+    """llmc_seq_fork: (1) a clone at the source's end decodes bit-identically to the source; (2) a fork of a prefix,
+    fed the rest of the prompt, matches the single-pass prefill; (3) shared full pages survive freeing either side and
+    the copied tail page keeps the two sequences' appended rows apart; (4) nothing leaks from the page pool."""
+    name = "tiny"
+    V = DIMS[name]["vocab"]
+    e = gpu.Engine(dims=DIMS[name], seed=6, max_ctx=256, max_slots=4, prefill_impl=DEFAULT_IMPL, flags=flags)
+    rng = np.random.default_rng(17)
+    prompt = rng.integers(0, V, 150)            # 2 full pages of 64 + 22 positions in the third
+    a = e.seq_alloc()
+    first, lg_full = e.prefill(a, prompt, want_logits=True)
+    b = e.seq_fork(a)                           # clone: 2 shared pages, copied tail, pending token inherited
+    assert e.seq_len(b) == 150 and e.get_next_token(b) == first
+    c = e.seq_fork(a, 100)                      # prefix: 1 shared page + 36 copied positions
+    assert e.seq_len(c) == 100
+    first_c, lg_c = e.prefill(c, prompt[100:], want_logits=True)
+    tol = TOL if not flags & 12 else 8e-2
+    assert np.abs(lg_c - lg_full).max() <= tol and e.seq_len(c) == 150
+    # the source and the clone decode one after the other (each appends to its own copy of the tail page)
+    out_a, lg_a = e.decode([a], 12, want_logits=True)
+    out_b, lg_b = e.decode([b], 12, want_logits=True)
+    assert out_a.tolist() == out_b.tolist() and np.array_equal(lg_a, lg_b)
+    # the source goes away; the clone still reads the pages they shared
+    e.seq_free(a)
+    d = e.seq_alloc()
+    assert e.prefill(d, prompt) == first
+    out_d1 = e.decode([d], 12)
+    out_b2, lg_b2 = e.decode([b], 6, want_logits=True)
+    out_d2, lg_d2 = e.decode([d], 6, want_logits=True)
+    assert out_d1.tolist() == out_a.tolist() and out_b2.tolist() == out_d2.tolist() and np.array_equal(lg_b2, lg_d2)
+    # oracle check of the clone's path
+    o = ref.Oracle(name, seed=6, max_ctx=256)
+    otoks, olog = o.generate(prompt, 19, want_logits=True)
+    gt = [first] + out_b[0].tolist() + out_b2[0].tolist()
+    where, margin = greedy_agreement(otoks, olog, gt, tol=tol)
+    assert where < 0, (where, margin)
+    # errors, and the pool: every page comes back
+    for bad in (0, 151 + 18):
+        with pytest.raises(gpu.LlmcError):
+            e.seq_fork(b, bad)
+    with pytest.raises(gpu.LlmcError):          # all four slots are in use: b, c, d and this one
+        x = e.seq_alloc()
+        e.seq_fork(b)
+    for s_ in (b, c, d, x):
+        e.seq_free(s_)
+    for rep in range(3):                        # 4 slots x 4 pages = the whole pool, three times over
+        ss = [e.seq_alloc() for _ in range(2)]
+        for s_ in ss:
+            e.prefill(s_, rng.integers(0, V, 250))
+        ff = [e.seq_fork(s_, 200) for s_ in ss]
+        for s_ in ff:
+            e.prefill(s_, rng.integers(0, V, 50))
+        for s_ in ss + ff:
+            e.seq_free(s_)
+    e.close()
+
+
 def test_error_paths(gpu):
     e = gpu.Engine(dims=DIMS["tiny"], seed=6, max_ctx=64, max_slots=2, prefill_impl=DEFAULT_IMPL)
     s = e.seq_alloc()

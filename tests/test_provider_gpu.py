@@ -105,6 +105,31 @@ def test_cli_duplicate_model_entries_share_one_engine(cli):
         assert doc["consensus"] == consensus
 
 
+def test_cli_prompt_cache_gives_the_answers_of_a_full_prefill(cli):
+    """The provider keeps the last prompt's KV cache per instance: duplicates of a model clone it (no prefill), and
+    the judge prompt -- which starts with the template's fixed head -- forks the common prefix.  The whole result.json
+    must be what the same run produces with the cache off (LLMC_PROMPT_CACHE=0): clones are bit-identical by
+    construction; the judge's forked-prefix prefill may round differently, so its text is only compared when the
+    oracle sees no near-tie among its greedy steps."""
+    prompt = "Name three prime numbers and say why each of them is prime."
+    args = [cli, "--models", "local-tiny,local-tiny,local-tiny-s1,local-tiny", "--judge", "local-tiny", "--max-new-tokens",
+            str(NEW), "--json", prompt]
+    docs = []
+    for cache in ("1", "0"):
+        env = dict(os.environ, LLMC_PROMPT_CACHE=cache)
+        r = subprocess.run(args, capture_output=True, text=True, timeout=300, env=env)
+        assert r.returncode == 0, r.stderr
+        docs.append(json.loads(r.stdout))
+    on, off = docs
+    key = lambda x: (x["model"], x["content"])
+    assert sorted(map(key, on["responses"])) == sorted(map(key, off["responses"]))
+    same_judge_input = [key(x) for x in on["responses"]] == [key(x) for x in off["responses"]]
+    rendered = orc.render_judge_prompt(prompt, on["responses"])
+    _, jm = oracle_answer(0, rendered)
+    if same_judge_input and jm > 1e-3:
+        assert on["consensus"] == off["consensus"]
+
+
 def test_cli_duplicates_decode_together_on_the_wide_path(cli):
     """Sixteen entries of the 1B model on one GPU: the provider's scheduler advances all sixteen sequences with one
     pass over the weights per step, so the fan-out takes a fraction of sixteen queries run one after another."""
