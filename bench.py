@@ -263,6 +263,39 @@ def decode_8b_leg(llmc, device, peak):
             "roofline_frac": algo / (step_ms / 1e3) / 1e9 / peak, "algorithmic_bytes_per_step": algo}
 
 
+def batch_sweep_leg(llmc, device, peak):
+    """BASELINE.json configs[4] (decode batch sweep) at the 1B shape on this GPU: B sequences, each prefilled with its
+    own 512-token prompt in fresh slots, 64 decode steps (context 512 -> 580); tok/s per GPU and the fraction of the HBM
+    roof on SURVEY section 8(d)'s bytes (weights + B x context x 32 KiB).  profiles/batch_sweep.py is the full sweep
+    (512 -> 768, both shapes, both KV formats)."""
+    out = {}
+    for B in (2, 8, 32, 128):
+        try:
+            eng = llmc.Engine(shape=llmc.SHAPE_LLAMA_1B, device=device, seed=0, max_ctx=640, max_slots=B)
+        except Exception as ex:
+            out[str(B)] = {"error": str(ex)[:200]}
+            continue
+        rng = np.random.default_rng(B)
+        slots = []
+        for _ in range(B):
+            sl = eng.seq_alloc()
+            eng.prefill(sl, rng.integers(0, 128256, PROMPT_LEN).astype(np.int32))
+            slots.append(sl)
+        eng.decode(slots, 4)                      # graph capture / first cooperative launch
+        ms = 0.0
+        for _ in range(4):
+            eng.decode(slots, 16)
+            ms += eng.stats()["last_decode_ms"]
+        st = eng.stats()
+        eng.close()
+        step_ms = ms / 64
+        ctx = PROMPT_LEN + 4 + 32
+        algo = st["weight_bytes"] + B * (ctx + 1) * 32768.0
+        out[str(B)] = {"ms_per_step": step_ms, "tok_s_per_gpu": B * 1e3 / step_ms,
+                       "roofline_frac": algo / (step_ms / 1e3) / 1e9 / peak}
+    return out
+
+
 def run_ours(args, rank, world, local_rank):
     import llm_consensus_b200.llmc as llmc
     ranks = Ranks(world, local_rank, "nccl")
@@ -351,6 +384,8 @@ def run_ours(args, rank, world, local_rank):
     if rank == 0 and not args.no_extra:
         # extra legs, outside the timed region (other ranks have released their GPUs at the barrier above)
         line["decode_8b"] = decode_8b_leg(llmc, local_rank, peak)
+        if world == 1:
+            line["batch_sweep_1b"] = batch_sweep_leg(llmc, local_rank, peak)
         line["consensus"] = consensus_leg(world)
         for k in ("consensus_runs_per_s", "fanout_ms", "judge_ms"):
             line[k] = line["consensus"].get(k)
@@ -370,7 +405,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
-    ap.add_argument("--no-extra", action="store_true", help="skip the 8B decode and consensus (config 3) legs")
+    ap.add_argument("--no-extra", action="store_true", help="skip the 8B decode, batch sweep (config 5) and consensus (config 3) legs")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
