@@ -20,6 +20,8 @@
 // boundary; the providers behind it are remote HTTP calls).
 #include "common.cuh"
 #include "kernels.h"
+#include <cstdlib>
+
 #include "attn_tile.cuh"
 
 namespace llmc {
@@ -244,6 +246,12 @@ template <int D, int G, typename KVT>
 cudaError_t launch_t(const AttnDecodeArgs& a, bool pdl, cudaStream_t s) {
   // two waves of blocks or more: small blocks, several resident per SM (measured: worse below that)
   if ((long long)a.nsplit * a.kv_heads * a.B >= 2 * 148) return launch_w<D, G, KVT, 4>(a, pdl, s);
+  // In between (batches of about 4..36 sequences): 8 warps.  A 16-warp block at 128 registers per thread fills the
+  // SM's register file, so the blocks of the NEXT kernel of the programmatic-launch chain (the O projection, which
+  // streams its first weight tiles before it waits) cannot become resident beside it; with 8 warps they can.  Measured
+  // 2-4 % per step at batches 8..32 on both shapes, contexts 512 and 2 048.  LLMC_ATTN_WARPS=16 restores 16.
+  static const int aw = getenv("LLMC_ATTN_WARPS") ? atoi(getenv("LLMC_ATTN_WARPS")) : 8;
+  if (aw == 8 && (long long)a.nsplit * a.kv_heads * a.B >= 32) return launch_w<D, G, KVT, 8>(a, pdl, s);
   return launch_w<D, G, KVT, AttnCfg<D, G>::AWARPS>(a, pdl, s);
 }
 
