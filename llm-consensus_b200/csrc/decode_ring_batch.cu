@@ -224,6 +224,35 @@ __global__ void __launch_bounds__(RTHREADS, 1) decode_ring_batch_kernel(const Me
 #pragma unroll
       for (int kb = 0; kb < 8; ++kb) to_frag(raw[p][kb], breg[p][kb][0], breg[p][kb][1]);
   };
+  // inputs that the previous phase left as bf16 planes (attention output, SwiGLU activation): this lane's part of its
+  // four k per 32-k block is one 8-byte load, already in fragment form
+  auto load_planes_raw = [&](uint2 (&raw)[NP][8], const uint16_t* hi, const uint16_t* lo, size_t stride, int koff) {
+    const uint16_t* plane = part ? lo : hi;
+#pragma unroll
+    for (int p = 0; p < NP; ++p) {
+      const int s = 2 * p + sl;
+#pragma unroll
+      for (int kb = 0; kb < 8; ++kb)
+        raw[p][kb] = s < B ? __ldcg(reinterpret_cast<const uint2*>(plane + (size_t)s * stride + koff + klane + kb * 32))
+                           : make_uint2(0u, 0u);
+    }
+  };
+  auto take_planes = [&](const uint2 (&raw)[NP][8]) {
+#pragma unroll
+    for (int p = 0; p < NP; ++p)
+#pragma unroll
+      for (int kb = 0; kb < 8; ++kb) {
+        breg[p][kb][0] = raw[p][kb].x;
+        breg[p][kb][1] = raw[p][kb].y;
+      }
+  };
+  auto load_planes = [&](const uint16_t* hi, const uint16_t* lo, size_t stride) {
+    const long long tx0 = stats ? clock64() : 0;
+    uint2 raw[NP][8];
+    load_planes_raw(raw, hi, lo, stride, 0);
+    take_planes(raw);
+    if (stats) t_x += clock64() - tx0 + (long long)(breg[0][0][0] == 0x12345678u);
+  };
   // K == SEG input with optional RMSNorm gain (sum of squares -> s_red, read by the epilogue side) and, in layer 0, the
   // embedding rows as the source (block 0 also writes them out as the residual stream)
   auto load_x = [&](const float* src, size_t stride, const uint16_t* gain, bool embed, bool write_x) {
@@ -373,12 +402,12 @@ __global__ void __launch_bounds__(RTHREADS, 1) decode_ring_batch_kernel(const Me
   };
   // K = nseg * SEG > SEG: segment-major over this block's (at most two) row groups, accumulators in registers; the next
   // segment's activation loads fly while this segment's slots run
-  auto run_phase_segs = [&](const RPhase& p, const float* src, size_t stride, auto&& epilogue) {
+  auto run_phase_segs = [&](const RPhase& p, const uint16_t* hi, const uint16_t* lo, size_t stride, auto&& epilogue) {
     const int nseg = p.K / SEG, ngroups = p.ntasks / 4;
     int first = (int)blockIdx.x - rot;
     if (first < 0) first += grid;
-    float4 raw[NP][8];
-    load_raw(raw, src, stride, 0);
+    uint2 raw[NP][8];
+    load_planes_raw(raw, hi, lo, stride, 0);
     float c0[NP][4], c1[NP][4];
 #pragma unroll
     for (int p2 = 0; p2 < NP; ++p2)
@@ -388,8 +417,8 @@ __global__ void __launch_bounds__(RTHREADS, 1) decode_ring_batch_kernel(const Me
 #pragma unroll
     for (int sg = 0; sg < MAXSEG; ++sg)
       if (sg < nseg) {
-        convert(raw);
-        if (sg + 1 < nseg) load_raw(raw, src, stride, (sg + 1) * SEG);
+        take_planes(raw);
+        if (sg + 1 < nseg) load_planes_raw(raw, hi, lo, stride, (sg + 1) * SEG);
         if (first < ngroups) {
           const unsigned r = seq % NSLOT, par = (seq / NSLOT) & 1u;
           ++seq;
@@ -517,7 +546,17 @@ __global__ void __launch_bounds__(RTHREADS, 1) decode_ring_batch_kernel(const Me
           }
           attn_write_record<D, G, KVT>(part_rec + (size_t)warp * G * PS, m, lsum, o);
           cbar();
-          float* out_row = a.attn + (size_t)at_s * QD;
+          // the result goes out as bf16 hi / mid planes, the form the O projection's fragments take
+          auto put_out = [&](int idx, const float (&v)[D / 32]) {
+            constexpr int DPL = D / 32;
+#pragma unroll
+            for (int i = 0; i < DPL; i += 2) {
+              const uint32_t h = pack2(v[i], v[i + 1]);
+              const uint32_t m = pack2(v[i] - bf16lo(h), v[i + 1] - bf16hi(h));
+              *reinterpret_cast<uint32_t*>(a.attn_hi + (size_t)at_s * QD + idx + i) = h;
+              *reinterpret_cast<uint32_t*>(a.attn_lo + (size_t)at_s * QD + idx + i) = m;
+            }
+          };
           float* scratch = a.attn_scratch + (size_t)(at_s * a.kv_heads + kvh) * nspb * G * PS;
           if (warp < G) {  // warp h merges head h over the block's warps
             constexpr int DPL = D / 32;
@@ -542,7 +581,8 @@ __global__ void __launch_bounds__(RTHREADS, 1) decode_ring_batch_kernel(const Me
             if (nsp == 1) {   // the block saw the whole context: done, no cross-block merge
               const float inv = 1.0f / L;
 #pragma unroll
-              for (int i = 0; i < DPL; ++i) out_row[(size_t)(kvh * G + h) * D + lane * DPL + i] = O[i] * inv;
+              for (int i = 0; i < DPL; ++i) O[i] *= inv;
+              put_out((kvh * G + h) * D + lane * DPL, O);
             } else {
               float* rec = scratch + ((size_t)split * G + h) * PS;
 #pragma unroll
@@ -592,7 +632,8 @@ __global__ void __launch_bounds__(RTHREADS, 1) decode_ring_batch_kernel(const Me
               }
               const float inv = 1.0f / L;
 #pragma unroll
-              for (int i = 0; i < DPL; ++i) out_row[(size_t)(kvh * G + h) * D + lane * DPL + i] = O[i] * inv;
+              for (int i = 0; i < DPL; ++i) O[i] *= inv;
+              put_out((kvh * G + h) * D + lane * DPL, O);
             };
             if (nsp <= 4) merge(std::integral_constant<int, 4>{});
             else if (nsp <= 8) merge(std::integral_constant<int, 8>{});
@@ -607,10 +648,10 @@ __global__ void __launch_bounds__(RTHREADS, 1) decode_ring_batch_kernel(const Me
       {
         const RPhase p = phase_desc(l, 1);
         if (p.K == SEG) {
-          load_x(a.attn, (size_t)QD, nullptr, false, false);
+          load_planes(a.attn_hi, a.attn_lo, (size_t)QD);
           run_phase(p, false, resid_epilogue);
         } else {
-          run_phase_segs(p, a.attn, (size_t)QD, resid_epilogue);
+          run_phase_segs(p, a.attn_hi, a.attn_lo, (size_t)QD, resid_epilogue);
         }
         grid_barrier();
       }
@@ -619,7 +660,12 @@ __global__ void __launch_bounds__(RTHREADS, 1) decode_ring_batch_kernel(const Me
       {
         load_x(a.x, (size_t)H, ly.g2, false, false);
         run_phase(phase_desc(l, 2), true, [&](int s, int g, float gt, float up) {
-          if (wl == 0) a.act[(size_t)s * I + g] = gt / (1.0f + __expf(-gt)) * up;
+          if (wl == 0) {
+            const float v = gt / (1.0f + __expf(-gt)) * up;
+            const uint16_t h = f32_to_bf16_bits(v);
+            a.act_hi[(size_t)s * I + g] = h;
+            a.act_lo[(size_t)s * I + g] = f32_to_bf16_bits(v - __uint_as_float((uint32_t)h << 16));
+          }
         });
         grid_barrier();
       }
@@ -628,10 +674,10 @@ __global__ void __launch_bounds__(RTHREADS, 1) decode_ring_batch_kernel(const Me
       {
         const RPhase p = phase_desc(l, 3);
         if (p.K == SEG) {
-          load_x(a.act, (size_t)I, nullptr, false, false);
+          load_planes(a.act_hi, a.act_lo, (size_t)I);
           run_phase(p, false, resid_epilogue);
         } else {
-          run_phase_segs(p, a.act, (size_t)I, resid_epilogue);
+          run_phase_segs(p, a.act_hi, a.act_lo, (size_t)I, resid_epilogue);
         }
         grid_barrier();
       }

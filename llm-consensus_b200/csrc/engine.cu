@@ -555,6 +555,10 @@ static int create_impl(llmc_engine* e, const llmc_config& c) {
       if (int rc = dalloc(e, &e->ringb_part_val, G4)) return rc;
       if (int rc = dalloc(e, &e->ringb_part_idx, G4)) return rc;
       if (int rc = dalloc(e, &e->ringb_counters, (size_t)4 * d.kv_heads)) return rc;
+      if (int rc = dalloc(e, &e->ringb_attn_hi, (size_t)4 * QD)) return rc;
+      if (int rc = dalloc(e, &e->ringb_attn_lo, (size_t)4 * QD)) return rc;
+      if (int rc = dalloc(e, &e->ringb_act_hi, (size_t)4 * I)) return rc;
+      if (int rc = dalloc(e, &e->ringb_act_lo, (size_t)4 * I)) return rc;
       E_TRY(cudaMemsetAsync(e->ringb_counters, 0, (size_t)4 * d.kv_heads * sizeof(unsigned), e->stream));
     }
     if (e->use_flow) {
@@ -842,6 +846,7 @@ static int decode_group(llmc_engine* e, const int32_t* slots, int32_t nslots, in
     m.attn_scratch = e->ringb_scratch; m.max_tiles = e->mega_max_tiles; m.attn_counters = e->ringb_counters;
     m.part_val = e->ringb_part_val; m.part_idx = e->ringb_part_idx; m.out_tokens = e->d_out_tokens; m.nsteps = nsteps;
     m.out_stride = MAX_STEPS_PER_CALL; m.slots = e->d_slots; m.B = nslots;
+    m.attn_hi = e->ringb_attn_hi; m.attn_lo = e->ringb_attn_lo; m.act_hi = e->ringb_act_hi; m.act_lo = e->ringb_act_lo;
     m.barrier = e->mega_barrier;
     {
       const char* tpb = getenv("LLMC_MEGA_TILES_PER_BLOCK");

@@ -134,6 +134,9 @@ struct MegaArgs {
   const int* slots;            // device [B]
   int B;
   int out_stride;              // out_tokens[seq * out_stride + step]
+  // attention output and SwiGLU activation of the B sequences as bf16 hi / mid planes ([B][QD], [B][I]): written once by
+  // the producing phase, read by every block of the next one without any conversion
+  uint16_t *attn_hi, *attn_lo, *act_hi, *act_lo;
 };
 cudaError_t launch_decode_mega(const MegaArgs& a, int sm_count, cudaStream_t s);
 // ------------------------------------------------------------------ decode_ring.cu
