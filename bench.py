@@ -349,7 +349,7 @@ def run_ours(args, rank, world, local_rank):
     peak, peak_src = peaks()
     achieved = bytes_per_step / step_s / 1e9
     traffic = None
-    tp = os.path.join(ROOT, "profiles", "r2_ring_traffic.json")
+    tp = os.path.join(ROOT, "profiles", "r2_ring_batch_traffic.json")
     if os.path.exists(tp):
         traffic = json.load(open(tp))["dram_bytes_per_step"]
     line = {
@@ -370,9 +370,10 @@ def run_ours(args, rank, world, local_rank):
         "gpu_launches": int(launches_all),
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                      "traffic": traffic, "peak_source": peak_src, "frac_of_8TBs_nominal": achieved / 8000.0,
-                     "kernel": "decode_ring_kernel: one persistent cooperative kernel runs every decode step of a "
-                               "llmc_decode call (5 phases/layer x 16 + LM head per step); figures are per step",
-                     "traffic_source": "profiles/r2_ring_traffic.json (ncu --set full of the round-2 build, (dram__bytes_read.sum + "
+                     "kernel": "decode_ring_batch_kernel<64,4,float,1> (the batched ring kernel with one sequence): one persistent "
+                               "cooperative kernel runs every decode step of a llmc_decode call (5 phases/layer x 16 + LM "
+                               "head per step); figures are per step",
+                     "traffic_source": "profiles/r2_ring_batch_traffic.json (ncu --set full of the round-2 build, (dram__bytes_read.sum + "
                                        "dram__bytes_write.sum) / steps)",
                      "algorithmic_bytes_per_launch": bytes_per_step, "avg_launch_us": step_s * 1e6},
         "clocks": clocks,

@@ -83,7 +83,7 @@ typedef struct llmc_config {
 #define LLMC_FLAG_NO_MEGAKERNEL 16 /* batch-1 decode as 81 kernels per step instead of one persistent kernel */
 #define LLMC_FLAG_RING_FLOW 64 /* experimental: ring kernel with tagged-word hand-overs (decode_flow.cu) instead of grid barriers between phases (decode_ring.cu) */
 #define LLMC_FLAG_RING_MMA 256 /* experimental: ring kernel with the slot arithmetic on mma.sync (decode_ring_mma.cu); same speed as the FMA loop, kept as a comparator */
-#define LLMC_FLAG_NO_RING_BATCH 128 /* 2..4 sequences decode through the per-step kernel graph instead of the persistent batched ring kernel (decode_ring_batch.cu) */
+#define LLMC_FLAG_NO_RING_BATCH 128 /* no decode_ring_batch.cu: batch 1 on decode_ring.cu (or decode_mega.cu), 2..4 sequences through the per-step kernel graph */
 #define LLMC_FLAG_NO_RING 32 /* persistent batch-1 decode pulls weights through registers (decode_mega.cu) instead of the TMA shared-memory ring (decode_ring.cu) */
 
 typedef struct llmc_stats {

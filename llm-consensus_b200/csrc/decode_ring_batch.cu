@@ -54,9 +54,11 @@ __device__ __forceinline__ uint32_t pack2(float lo, float hi) {
   return r;
 }
 
-// NP = pairs of sequences (1: batch 2; 2: batch 3 or 4)
-template <int D, int G, typename KVT, int NP>
+// NP = pairs of sequences (1: batch 2; 2: batch 3 or 4).  ONE (with NP = 1): a single sequence whose activation takes
+// three of the four columns of a half -- hi, mid, lo: 24 mantissa bits, every product exact as in the FMA kernels.
+template <int D, int G, typename KVT, int NP, bool ONE = false>
 __global__ void __launch_bounds__(RTHREADS, 1) decode_ring_batch_kernel(const MegaArgs a) {
+  static_assert(!ONE || NP == 1, "the single-sequence variant uses one column group");
   constexpr int NB = 2 * NP;
   constexpr int PS = D + 2;
   constexpr int hd2 = D / 2;
@@ -158,7 +160,9 @@ __global__ void __launch_bounds__(RTHREADS, 1) decode_ring_batch_kernel(const Me
   // fragment coordinates: B column / A row fg, k slot ft.  Column fg = 4 half + 2 sl + part: half = which four of the
   // lane's eight k, sl = sequence of the pair, part = hi / mid.
   const int fg = lane >> 2, ft = lane & 3;
-  const int half = fg >> 2, sl = (fg >> 1) & 1, part = fg & 1;
+  // (ONE: column = 4 half + part, part 3 unused)
+  const int half = fg >> 2, sl = ONE ? 0 : (fg >> 1) & 1, part = ONE ? (fg & 3) : (fg & 1);
+  const bool col_live = !ONE || part < 3;
   const int klane = warp * 256 + ft * 8 + half * 4;   // + 32 kb: the four k this lane supplies per 32-k block
   // the finishing side: a warp's 32 lanes are four groups of 8 (one lane per consumer warp's partial sum); group j works
   // for sequence myseq
@@ -205,15 +209,22 @@ __global__ void __launch_bounds__(RTHREADS, 1) decode_ring_batch_kernel(const Me
       const int s = 2 * p + sl;
 #pragma unroll
       for (int kb = 0; kb < 8; ++kb)
-        raw[p][kb] = s < B ? __ldcg(reinterpret_cast<const float4*>(src + (size_t)s * stride + koff + klane + kb * 32))
+        raw[p][kb] = (s < B && col_live) ? __ldcg(reinterpret_cast<const float4*>(src + (size_t)s * stride + koff + klane + kb * 32))
                            : make_float4(0.f, 0.f, 0.f, 0.f);
     }
   };
   auto to_frag = [&](const float4& v, uint32_t& b0, uint32_t& b1) {
     uint32_t h0 = pack2(v.x, v.y), h1 = pack2(v.z, v.w);
     if (part) {
-      h0 = pack2(v.x - bf16lo(h0), v.y - bf16hi(h0));
-      h1 = pack2(v.z - bf16lo(h1), v.w - bf16hi(h1));
+      float r0 = v.x - bf16lo(h0), r1 = v.y - bf16hi(h0), r2 = v.z - bf16lo(h1), r3 = v.w - bf16hi(h1);
+      h0 = pack2(r0, r1);
+      h1 = pack2(r2, r3);
+      if constexpr (ONE) {
+        if (part == 2) {
+          h0 = pack2(r0 - bf16lo(h0), r1 - bf16hi(h0));
+          h1 = pack2(r2 - bf16lo(h1), r3 - bf16hi(h1));
+        }
+      }
     }
     b0 = h0;
     b1 = h1;
@@ -226,14 +237,14 @@ __global__ void __launch_bounds__(RTHREADS, 1) decode_ring_batch_kernel(const Me
   };
   // inputs that the previous phase left as bf16 planes (attention output, SwiGLU activation): this lane's part of its
   // four k per 32-k block is one 8-byte load, already in fragment form
-  auto load_planes_raw = [&](uint2 (&raw)[NP][8], const uint16_t* hi, const uint16_t* lo, size_t stride, int koff) {
-    const uint16_t* plane = part ? lo : hi;
+  auto load_planes_raw = [&](uint2 (&raw)[NP][8], const uint16_t* hi, const uint16_t* lo, const uint16_t* lo2, size_t stride, int koff) {
+    const uint16_t* plane = part == 0 ? hi : part == 1 ? lo : lo2;
 #pragma unroll
     for (int p = 0; p < NP; ++p) {
       const int s = 2 * p + sl;
 #pragma unroll
       for (int kb = 0; kb < 8; ++kb)
-        raw[p][kb] = s < B ? __ldcg(reinterpret_cast<const uint2*>(plane + (size_t)s * stride + koff + klane + kb * 32))
+        raw[p][kb] = (s < B && col_live) ? __ldcg(reinterpret_cast<const uint2*>(plane + (size_t)s * stride + koff + klane + kb * 32))
                            : make_uint2(0u, 0u);
     }
   };
@@ -246,10 +257,10 @@ __global__ void __launch_bounds__(RTHREADS, 1) decode_ring_batch_kernel(const Me
         breg[p][kb][1] = raw[p][kb].y;
       }
   };
-  auto load_planes = [&](const uint16_t* hi, const uint16_t* lo, size_t stride) {
+  auto load_planes = [&](const uint16_t* hi, const uint16_t* lo, const uint16_t* lo2, size_t stride) {
     const long long tx0 = stats ? clock64() : 0;
     uint2 raw[NP][8];
-    load_planes_raw(raw, hi, lo, stride, 0);
+    load_planes_raw(raw, hi, lo, lo2, stride, 0);
     take_planes(raw);
     if (stats) t_x += clock64() - tx0 + (long long)(breg[0][0][0] == 0x12345678u);
   };
@@ -266,7 +277,7 @@ __global__ void __launch_bounds__(RTHREADS, 1) decode_ring_batch_kernel(const Me
 #pragma unroll
         for (int kb = 0; kb < 8; ++kb) {
           float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
-          if (s < B) {
+          if (s < B && col_live) {
             const uint2 e = *reinterpret_cast<const uint2*>(er + klane + kb * 32);
             v = make_float4(bf16lo(e.x), bf16hi(e.x), bf16lo(e.y), bf16hi(e.y));
             if (write_x && part == 0) *reinterpret_cast<float4*>(a.x + (size_t)s * H + klane + kb * 32) = v;
@@ -342,7 +353,12 @@ __global__ void __launch_bounds__(RTHREADS, 1) decode_ring_batch_kernel(const Me
     for (int p = 0; p < NP; ++p) {
       float v = ft < 2 ? c[p][0] + c[p][1] : c[p][2] + c[p][3];
       v += __shfl_xor_sync(0xffffffffu, v, 2);   // first-half + second-half columns of the same sequence
-      if (ft < 2) s_acc[warp][pend][2 * p + ft][fg] = v;
+      if constexpr (ONE) {
+        v += __shfl_xor_sync(0xffffffffu, v, 1);   // (hi, mid) + (lo, unused)
+        if (ft == 0) s_acc[warp][pend][0][fg] = v;
+      } else {
+        if (ft < 2) s_acc[warp][pend][2 * p + ft][fg] = v;
+      }
     }
     if (pend == 0) pend_rg0 = rg;
     ++pend;
@@ -402,12 +418,12 @@ __global__ void __launch_bounds__(RTHREADS, 1) decode_ring_batch_kernel(const Me
   };
   // K = nseg * SEG > SEG: segment-major over this block's (at most two) row groups, accumulators in registers; the next
   // segment's activation loads fly while this segment's slots run
-  auto run_phase_segs = [&](const RPhase& p, const uint16_t* hi, const uint16_t* lo, size_t stride, auto&& epilogue) {
+  auto run_phase_segs = [&](const RPhase& p, const uint16_t* hi, const uint16_t* lo, const uint16_t* lo2, size_t stride, auto&& epilogue) {
     const int nseg = p.K / SEG, ngroups = p.ntasks / 4;
     int first = (int)blockIdx.x - rot;
     if (first < 0) first += grid;
     uint2 raw[NP][8];
-    load_planes_raw(raw, hi, lo, stride, 0);
+    load_planes_raw(raw, hi, lo, lo2, stride, 0);
     float c0[NP][4], c1[NP][4];
 #pragma unroll
     for (int p2 = 0; p2 < NP; ++p2)
@@ -418,7 +434,7 @@ __global__ void __launch_bounds__(RTHREADS, 1) decode_ring_batch_kernel(const Me
     for (int sg = 0; sg < MAXSEG; ++sg)
       if (sg < nseg) {
         take_planes(raw);
-        if (sg + 1 < nseg) load_planes_raw(raw, hi, lo, stride, (sg + 1) * SEG);
+        if (sg + 1 < nseg) load_planes_raw(raw, hi, lo, lo2, stride, (sg + 1) * SEG);
         if (first < ngroups) {
           const unsigned r = seq % NSLOT, par = (seq / NSLOT) & 1u;
           ++seq;
@@ -552,9 +568,12 @@ __global__ void __launch_bounds__(RTHREADS, 1) decode_ring_batch_kernel(const Me
 #pragma unroll
             for (int i = 0; i < DPL; i += 2) {
               const uint32_t h = pack2(v[i], v[i + 1]);
-              const uint32_t m = pack2(v[i] - bf16lo(h), v[i + 1] - bf16hi(h));
+              const float r0 = v[i] - bf16lo(h), r1 = v[i + 1] - bf16hi(h);
+              const uint32_t m = pack2(r0, r1);
               *reinterpret_cast<uint32_t*>(a.attn_hi + (size_t)at_s * QD + idx + i) = h;
               *reinterpret_cast<uint32_t*>(a.attn_lo + (size_t)at_s * QD + idx + i) = m;
+              if constexpr (ONE)
+                *reinterpret_cast<uint32_t*>(a.attn_lo2 + (size_t)at_s * QD + idx + i) = pack2(r0 - bf16lo(m), r1 - bf16hi(m));
             }
           };
           float* scratch = a.attn_scratch + (size_t)(at_s * a.kv_heads + kvh) * nspb * G * PS;
@@ -648,10 +667,10 @@ __global__ void __launch_bounds__(RTHREADS, 1) decode_ring_batch_kernel(const Me
       {
         const RPhase p = phase_desc(l, 1);
         if (p.K == SEG) {
-          load_planes(a.attn_hi, a.attn_lo, (size_t)QD);
+          load_planes(a.attn_hi, a.attn_lo, a.attn_lo2, (size_t)QD);
           run_phase(p, false, resid_epilogue);
         } else {
-          run_phase_segs(p, a.attn_hi, a.attn_lo, (size_t)QD, resid_epilogue);
+          run_phase_segs(p, a.attn_hi, a.attn_lo, a.attn_lo2, (size_t)QD, resid_epilogue);
         }
         grid_barrier();
       }
@@ -663,8 +682,11 @@ __global__ void __launch_bounds__(RTHREADS, 1) decode_ring_batch_kernel(const Me
           if (wl == 0) {
             const float v = gt / (1.0f + __expf(-gt)) * up;
             const uint16_t h = f32_to_bf16_bits(v);
+            const float r = v - __uint_as_float((uint32_t)h << 16);
+            const uint16_t m = f32_to_bf16_bits(r);
             a.act_hi[(size_t)s * I + g] = h;
-            a.act_lo[(size_t)s * I + g] = f32_to_bf16_bits(v - __uint_as_float((uint32_t)h << 16));
+            a.act_lo[(size_t)s * I + g] = m;
+            if constexpr (ONE) a.act_lo2[(size_t)s * I + g] = f32_to_bf16_bits(r - __uint_as_float((uint32_t)m << 16));
           }
         });
         grid_barrier();
@@ -674,10 +696,10 @@ __global__ void __launch_bounds__(RTHREADS, 1) decode_ring_batch_kernel(const Me
       {
         const RPhase p = phase_desc(l, 3);
         if (p.K == SEG) {
-          load_planes(a.act_hi, a.act_lo, (size_t)I);
+          load_planes(a.act_hi, a.act_lo, a.act_lo2, (size_t)I);
           run_phase(p, false, resid_epilogue);
         } else {
-          run_phase_segs(p, a.act_hi, a.act_lo, (size_t)I, resid_epilogue);
+          run_phase_segs(p, a.act_hi, a.act_lo, a.act_lo2, (size_t)I, resid_epilogue);
         }
         grid_barrier();
       }
@@ -760,9 +782,9 @@ size_t ringb_smem_bytes(int G, int D) {
 // static shared memory of the kernel (s_acc, s_rope and the small arrays), upper bound
 size_t ringb_static_bytes(int D) { return (size_t)RW * NGB * 4 * 8 * 4 + (size_t)4 * 2 * (D / 2) * 4 + 1024; }
 
-template <int D, int G, typename KVT, int NP>
+template <int D, int G, typename KVT, int NP, bool ONE = false>
 cudaError_t launch_t(const MegaArgs& a, int grid, cudaStream_t s) {
-  auto kern = decode_ring_batch_kernel<D, G, KVT, NP>;
+  auto kern = decode_ring_batch_kernel<D, G, KVT, NP, ONE>;
   const size_t smem = ringb_smem_bytes(G, D);
   cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   if (e != cudaSuccess) return e;
@@ -773,6 +795,10 @@ cudaError_t launch_t(const MegaArgs& a, int grid, cudaStream_t s) {
 
 template <int D, int G, typename KVT>
 cudaError_t launch_np(const MegaArgs& a, int grid, cudaStream_t s) {
+  // batch 1: the two-part kernel with the second sequence absent (16 mantissa bits of the activations, like every
+  // batched path) measured 0.630 ms per step, the three-part variant (24 bits) 0.650 -- LLMC_RINGB_ONE=1 selects it
+  static const bool one = getenv("LLMC_RINGB_ONE") != nullptr && atoi(getenv("LLMC_RINGB_ONE")) != 0;
+  if (a.B == 1 && one) return launch_t<D, G, KVT, 1, true>(a, grid, s);
   static const bool force2 = getenv("LLMC_RINGB_NP2") != nullptr;   // experiment knob: the two-pair kernel for batch 2 as well
   return (a.B <= 2 && !force2) ? launch_t<D, G, KVT, 1>(a, grid, s) : launch_t<D, G, KVT, 2>(a, grid, s);
 }
@@ -792,7 +818,7 @@ bool seg_ok(int K) { return K == SEG || K == 2 * SEG || K == 4 * SEG; }
 
 bool decode_ring_batch_supported(int B, int H, int QD, int KD, int I, int V, int q_heads, int kv_heads, int head_dim,
                                  int sm_count) {
-  if (B < 1 || B > 4) return false;   // (1: experiment knob LLMC_RING_BATCH_B1)
+  if (B < 1 || B > 4) return false;
   if (kv_heads < 1 || q_heads % kv_heads || q_heads / kv_heads != 4) return false;
   if (!(head_dim == 64 || head_dim == 128)) return false;
   if (H != SEG || !seg_ok(QD) || !seg_ok(I)) return false;

@@ -559,6 +559,8 @@ static int create_impl(llmc_engine* e, const llmc_config& c) {
       if (int rc = dalloc(e, &e->ringb_attn_lo, (size_t)4 * QD)) return rc;
       if (int rc = dalloc(e, &e->ringb_act_hi, (size_t)4 * I)) return rc;
       if (int rc = dalloc(e, &e->ringb_act_lo, (size_t)4 * I)) return rc;
+      if (int rc = dalloc(e, &e->ringb_attn_lo2, (size_t)QD)) return rc;
+      if (int rc = dalloc(e, &e->ringb_act_lo2, (size_t)I)) return rc;
       E_TRY(cudaMemsetAsync(e->ringb_counters, 0, (size_t)4 * d.kv_heads * sizeof(unsigned), e->stream));
     }
     if (e->use_flow) {
@@ -587,7 +589,7 @@ static int create_impl(llmc_engine* e, const llmc_config& c) {
   E_TRY(cudaGetLastError());
   stage("workspaces, sync");
   if (init_trace)
-    fprintf(stderr, "[init dev %d] 2..4 sequences: %s\n", c.device, e->use_ringb ? "decode_ring_batch (persistent)" : "kernel graph per step");
+    fprintf(stderr, "[init dev %d] 1..4 sequences: %s\n", c.device, e->use_ringb ? "decode_ring_batch (persistent; batch 1 unless LLMC_RING_BATCH_B1=0 or an experimental ring flag)" : "kernel graph per step (batch 1: below)");
   if (init_trace)
     fprintf(stderr, "[init dev %d] batch-1 decode path: %s\n", c.device,
             !e->use_mega ? "kernel graph" : e->use_flow ? "decode_flow (ring, tagged-word hand-overs)" : e->use_ring_mma ? "decode_ring_mma (ring, mma.sync slots)"
@@ -824,8 +826,11 @@ static int decode_group(llmc_engine* e, const int32_t* slots, int32_t nslots, in
   // context it will reach (the graph is keyed by it)
   const int nsplit = attn_decode_nsplit(max_len + nsteps);
   cudaGraphExec_t ge = nullptr;
-  static const bool ringb_b1 = getenv("LLMC_RING_BATCH_B1") != nullptr;   // experiment knob: batch 1 through the batched kernel
-  const bool ringb = e->use_ringb && nslots >= (ringb_b1 ? 1 : 2) && nslots <= 4 && decode_ring_batch_supported(nslots, d.hidden, d.qd(), d.kd(), d.inter, d.vocab, d.q_heads, d.kv_heads,
+  // batch 1 takes the batched kernel too (second sequence absent): 0.632 ms per step at the 1B shape against 0.655 for
+  // decode_ring.cu; LLMC_RING_BATCH_B1=0 (or the experimental ring flags) keeps batch 1 on the single-sequence kernels
+  static const bool ringb_b1 = !(getenv("LLMC_RING_BATCH_B1") && atoi(getenv("LLMC_RING_BATCH_B1")) == 0);
+  const bool b1_ok = ringb_b1 && !e->use_flow && !e->use_ring_mma;
+  const bool ringb = e->use_ringb && nslots >= (b1_ok ? 1 : 2) && nslots <= 4 && decode_ring_batch_supported(nslots, d.hidden, d.qd(), d.kd(), d.inter, d.vocab, d.q_heads, d.kv_heads,
                                                  d.head_dim, e->prop.multiProcessorCount);
   if (e->use_graph && !(e->use_mega && nslots == 1) && !ringb) {
     int rc = get_graph(e, nslots, want_logits, nsplit, &ge);
@@ -847,6 +852,7 @@ static int decode_group(llmc_engine* e, const int32_t* slots, int32_t nslots, in
     m.part_val = e->ringb_part_val; m.part_idx = e->ringb_part_idx; m.out_tokens = e->d_out_tokens; m.nsteps = nsteps;
     m.out_stride = MAX_STEPS_PER_CALL; m.slots = e->d_slots; m.B = nslots;
     m.attn_hi = e->ringb_attn_hi; m.attn_lo = e->ringb_attn_lo; m.act_hi = e->ringb_act_hi; m.act_lo = e->ringb_act_lo;
+    m.attn_lo2 = e->ringb_attn_lo2; m.act_lo2 = e->ringb_act_lo2;
     m.barrier = e->mega_barrier;
     {
       const char* tpb = getenv("LLMC_MEGA_TILES_PER_BLOCK");

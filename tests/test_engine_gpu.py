@@ -114,7 +114,7 @@ def test_teacher_forced_decode_logits(gpu, name, flags):
 WIDE = ["wide-1b", "wide-d128", "wide-mha"]
 
 
-@pytest.mark.parametrize("flags", [0, 64, 256, 32, 4, 68, 260, 36])   # 0: ring kernel (grid barriers); 64: ring kernel, tagged-word hand-overs; 256: ring kernel, mma.sync slots; 32: register-streaming kernel; 4: bf16 KV
+@pytest.mark.parametrize("flags", [0, 128, 64, 256, 32, 4, 132, 68, 260, 36])   # 0: batched ring kernel with one sequence; 128: decode_ring (FMA slots, grid barriers); 64: tagged-word hand-overs; 256: mma.sync slots; 32: register-streaming kernel; 4: bf16 KV
 @pytest.mark.parametrize("name", WIDE)
 def test_ring_decode_teacher_forced_logits(gpu, name, flags):
     """The persistent decode kernels at hidden = 2048 (the ring kernel's shapes: rows of 2048 / 4096 / 8192
@@ -138,7 +138,7 @@ def test_ring_decode_teacher_forced_logits(gpu, name, flags):
     e.close()
 
 
-@pytest.mark.parametrize("flags", [0, 64, 256, 32])
+@pytest.mark.parametrize("flags", [0, 128, 64, 256, 32])
 def test_persistent_decode_long_context(gpu, flags):
     """Attention phase of the persistent kernels over a long context (2 300 positions: 72 tiles = the 8-way split cap,
     several tiles per warp, chunked prefill before it), teacher-forced against the oracle."""
