@@ -69,6 +69,7 @@ __global__ void __launch_bounds__(RTHREADS, 1) decode_ring_batch_kernel(const Me
   __shared__ float s_acc[RW][NGB][NB][8];   // [warp][row group of the batch][sequence][row]
   __shared__ float s_rope[NB][2][hd2];      // this step's RoPE rows (cos, sin) of each sequence
   __shared__ float s_red[RW][NB];           // sum of squares per warp and sequence
+  __shared__ float s_ss[RW][NB];            // ... of the rows a residual phase finished in this block
   __shared__ float s_val[RW][NB];
   __shared__ int s_idx[RW][NB];
   __shared__ int s_tok[NB], s_slot[NB], s_pos0[NB];
@@ -347,6 +348,8 @@ __global__ void __launch_bounds__(RTHREADS, 1) decode_ring_batch_kernel(const Me
   };
   // lane (fg, ft) holds C[row fg][cols 2ft, 2ft+1] in c[0], c[1] and C[row fg + 8][same cols] in c[2], c[3].  Useful:
   // rows 0..7 x columns 0..3 and rows 8..15 x columns 4..7; sequence sl of the pair: columns 2 sl, 2 sl + 1 (+ 4).
+  float rs_given = 1.f;       // 1/rms of sequence myseq when the input came as pre-scaled planes (load_xn)
+  bool rs_is_given = false;
   int pend = 0, pend_rg0 = 0;
   auto put_group = [&](float (&c)[NP][4], int rg) {
 #pragma unroll
@@ -371,10 +374,14 @@ __global__ void __launch_bounds__(RTHREADS, 1) decode_ring_batch_kernel(const Me
     cbar();
     float rs = 1.f;
     if (norm) {
-      float t = 0.f;
+      if (rs_is_given) {
+        rs = rs_given;
+      } else {
+        float t = 0.f;
 #pragma unroll
-      for (int w = 0; w < RW; ++w) t += s_red[w][myseq];
-      rs = rsqrtf(t / (float)K + a.eps);
+        for (int w = 0; w < RW; ++w) t += s_red[w][myseq];
+        rs = rsqrtf(t / (float)K + a.eps);
+      }
     }
     for (int pi0 = warp * PPP; pi0 < 4 * pend; pi0 += RW * PPP) {
       const int pi = pi0 + pi_off;   // (4 * pend is a multiple of PPP: never past the end)
@@ -453,12 +460,76 @@ __global__ void __launch_bounds__(RTHREADS, 1) decode_ring_batch_kernel(const Me
     flush_groups(false, p.K, epilogue);
     rot = (rot + ngroups) % grid;
   };
-  auto resid_epilogue = [&](int s, int task, float v0, float v1) {
-    // one writer per row and sequence: a fire-and-forget reduction (RED) gives the same fp32 sum as load-add-store
-    if (wl == 0) {
-      atomicAdd(a.x + (size_t)s * H + 2 * task, v0);
-      atomicAdd(a.x + (size_t)s * H + 2 * task + 1, v1);
+  // ---- residual phases (O and down projection): x += W y.  Every row pair has ONE finishing lane group per sequence,
+  // so the update is load - add - store, with the old value requested at the start of the phase.  The same lane then
+  // leaves the new value, multiplied by the gain of the RMSNorm that reads it next, as bf16 hi / mid planes -- the
+  // form in which the next phase's fragments are loaded -- and adds its square to this block's share of the sum.
+  constexpr bool XN = !ONE;   // (the three-part variant keeps converting the fp32 stream itself)
+  float2 xo = make_float2(0.f, 0.f);
+  uint32_t gpair = 0u;
+  float ssl = 0.f;
+  int rphase = 0;   // residual phases done so far in this launch
+  auto resid_prefetch = [&](const RPhase& p, const uint16_t* gain_next) {
+    if constexpr (XN) {
+      const int ngroups = p.ntasks / 4;
+      int first = (int)blockIdx.x - rot;
+      if (first < 0) first += grid;
+      const int mypend = (first < ngroups ? 1 : 0) + (first + grid < ngroups ? 1 : 0);
+      const int pi = warp * PPP + pi_off;   // the one exchange of the phase: this lane group's row pair (flush_groups)
+      ssl = 0.f;
+      if (pi < 4 * mypend && myseq < B && wl == 0) {
+        const int task = (first + (pi >> 2) * grid) * 4 + (pi & 3);
+        xo = __ldcg(reinterpret_cast<const float2*>(a.x + (size_t)myseq * H + 2 * task));
+        gpair = *reinterpret_cast<const uint32_t*>(gain_next + 2 * task);
+      }
     }
+  };
+  auto resid_epilogue = [&](int s, int task, float v0, float v1) {
+    if (wl == 0) {
+      if constexpr (XN) {
+        const float x0 = xo.x + v0, x1 = xo.y + v1;
+        *reinterpret_cast<float2*>(a.x + (size_t)s * H + 2 * task) = make_float2(x0, x1);
+        ssl = x0 * x0 + x1 * x1;
+        const float y0 = x0 * bf16lo(gpair), y1 = x1 * bf16hi(gpair);
+        const uint32_t h = pack2(y0, y1);
+        *reinterpret_cast<uint32_t*>(a.xn_hi + (size_t)s * H + 2 * task) = h;
+        *reinterpret_cast<uint32_t*>(a.xn_lo + (size_t)s * H + 2 * task) = pack2(y0 - bf16lo(h), y1 - bf16hi(h));
+      } else {
+        // one writer per row and sequence: a fire-and-forget reduction (RED) gives the same fp32 sum as load-add-store
+        atomicAdd(a.x + (size_t)s * H + 2 * task, v0);
+        atomicAdd(a.x + (size_t)s * H + 2 * task + 1, v1);
+      }
+    }
+  };
+  // this block's share of sum(x^2) per sequence -> ss_part[seq][block] (zero when it finished no row)
+  auto resid_finish = [&]() {
+    if constexpr (XN) {
+      float t = ssl;
+      if constexpr (NB == 2) t += __shfl_xor_sync(0xffffffffu, t, 16);   // lane groups j and j + 2: the same sequence
+      if (wl == 0 && lj < NB) s_ss[warp][myseq] = t;
+      cbar();
+      // The blocks' shares meet in a 64-bit fixed-point accumulator (integer addition is associative, so the total does
+      // not depend on the order of arrival: deterministic) -- one 8-byte word per sequence for every reader, where 148
+      // per-block floats would be a hot spot in L2 (measured: + 2 us per reading phase).  Four slots used in turn;
+      // block 0 clears the one that is written two residual phases from now.
+      if (tid < NB) {
+        float u = 0.f;
+#pragma unroll
+        for (int w = 0; w < RW; ++w) u += s_ss[w][tid];
+        atomicAdd(a.ss_acc + (rphase & 3) * 4 + tid, __float2ull_rn(u * 16777216.0f));
+        if (blockIdx.x == 0) a.ss_acc[((rphase + 2) & 3) * 4 + tid] = 0ull;
+      }
+      ssl = 0.f;
+      ++rphase;
+    }
+  };
+  // RMSNorm input of the phases after a residual phase: finished fragments + 1/rms from the blocks' shares
+  auto load_xn = [&]() {
+    load_planes(a.xn_hi, a.xn_lo, nullptr, (size_t)H);
+    const unsigned long long acc = myseq < B ? __ldcg(a.ss_acc + ((rphase - 1) & 3) * 4 + myseq) : 0ull;
+    const float t = (float)acc * (1.0f / 16777216.0f);
+    rs_given = rsqrtf(t / (float)H + a.eps);
+    rs_is_given = true;
   };
 
   for (int step = 0; step < a.nsteps; ++step) {
@@ -487,7 +558,12 @@ __global__ void __launch_bounds__(RTHREADS, 1) decode_ring_batch_kernel(const Me
 
       // ---------------- P1: RMSNorm -> QKV -> RoPE -> KV append
       {
-        load_x(a.x, (size_t)H, ly.g1, l == 0, l == 0 && blockIdx.x == 0);
+        if (XN && l > 0) {
+          load_xn();
+        } else {
+          rs_is_given = false;
+          load_x(a.x, (size_t)H, ly.g1, l == 0, l == 0 && blockIdx.x == 0);
+        }
         run_phase(phase_desc(l, 0), true, [&](int s, int g, float v0, float v1) {
           const int h = g / hd2, i = g - h * hd2;
           if (h < a.q_heads + a.kv_heads) {
@@ -666,18 +742,25 @@ __global__ void __launch_bounds__(RTHREADS, 1) decode_ring_batch_kernel(const Me
       // ---------------- P3: x += Wo attn
       {
         const RPhase p = phase_desc(l, 1);
+        resid_prefetch(p, ly.g2);
         if (p.K == SEG) {
           load_planes(a.attn_hi, a.attn_lo, a.attn_lo2, (size_t)QD);
           run_phase(p, false, resid_epilogue);
         } else {
           run_phase_segs(p, a.attn_hi, a.attn_lo, a.attn_lo2, (size_t)QD, resid_epilogue);
         }
+        resid_finish();
         grid_barrier();
       }
 
       // ---------------- P4: act = silu(Wg h) * (Wu h), h = RMSNorm(x)
       {
-        load_x(a.x, (size_t)H, ly.g2, false, false);
+        if constexpr (XN) {
+          load_xn();
+        } else {
+          rs_is_given = false;
+          load_x(a.x, (size_t)H, ly.g2, false, false);
+        }
         run_phase(phase_desc(l, 2), true, [&](int s, int g, float gt, float up) {
           if (wl == 0) {
             const float v = gt / (1.0f + __expf(-gt)) * up;
@@ -695,19 +778,26 @@ __global__ void __launch_bounds__(RTHREADS, 1) decode_ring_batch_kernel(const Me
       // ---------------- P5: x += Wd act
       {
         const RPhase p = phase_desc(l, 3);
+        resid_prefetch(p, l + 1 < a.L ? a.layers[l + 1].g1 : a.gf);
         if (p.K == SEG) {
           load_planes(a.act_hi, a.act_lo, a.act_lo2, (size_t)I);
           run_phase(p, false, resid_epilogue);
         } else {
           run_phase_segs(p, a.act_hi, a.act_lo, a.act_lo2, (size_t)I, resid_epilogue);
         }
+        resid_finish();
         grid_barrier();
       }
     }
 
     // ---------------- LM head + greedy argmax per sequence (lowest index wins ties)
     {
-      load_x(a.x, (size_t)H, a.gf, false, false);
+      if constexpr (XN) {
+        load_xn();
+      } else {
+        rs_is_given = false;
+        load_x(a.x, (size_t)H, a.gf, false, false);
+      }
       float best = -INFINITY;   // of sequence myseq, over the row pairs this lane group finished
       int bi = 0x7fffffff;
       const bool store_logits = a.logits != nullptr && step == a.nsteps - 1;
@@ -823,7 +913,7 @@ bool decode_ring_batch_supported(int B, int H, int QD, int KD, int I, int V, int
   if (!(head_dim == 64 || head_dim == 128)) return false;
   if (H != SEG || !seg_ok(QD) || !seg_ok(I)) return false;
   if (((QD + 2 * KD) / 2) % 4 || V % 8 || I % 64) return false;
-  if (H / 8 > 2 * sm_count || B * kv_heads > sm_count) return false;
+  if (H / 8 > 2 * sm_count || B * kv_heads > sm_count || sm_count > 192) return false;
   return ringb_smem_bytes(4, head_dim) + ringb_static_bytes(head_dim) <= 227 * 1024;
 }
 

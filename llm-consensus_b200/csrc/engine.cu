@@ -559,6 +559,9 @@ static int create_impl(llmc_engine* e, const llmc_config& c) {
       if (int rc = dalloc(e, &e->ringb_attn_lo, (size_t)4 * QD)) return rc;
       if (int rc = dalloc(e, &e->ringb_act_hi, (size_t)4 * I)) return rc;
       if (int rc = dalloc(e, &e->ringb_act_lo, (size_t)4 * I)) return rc;
+      if (int rc = dalloc(e, &e->ringb_xn_hi, (size_t)4 * H)) return rc;
+      if (int rc = dalloc(e, &e->ringb_xn_lo, (size_t)4 * H)) return rc;
+      if (int rc = dalloc(e, &e->ringb_ss_acc, (size_t)16)) return rc;
       if (int rc = dalloc(e, &e->ringb_attn_lo2, (size_t)QD)) return rc;
       if (int rc = dalloc(e, &e->ringb_act_lo2, (size_t)I)) return rc;
       E_TRY(cudaMemsetAsync(e->ringb_counters, 0, (size_t)4 * d.kv_heads * sizeof(unsigned), e->stream));
@@ -853,6 +856,8 @@ static int decode_group(llmc_engine* e, const int32_t* slots, int32_t nslots, in
     m.out_stride = MAX_STEPS_PER_CALL; m.slots = e->d_slots; m.B = nslots;
     m.attn_hi = e->ringb_attn_hi; m.attn_lo = e->ringb_attn_lo; m.act_hi = e->ringb_act_hi; m.act_lo = e->ringb_act_lo;
     m.attn_lo2 = e->ringb_attn_lo2; m.act_lo2 = e->ringb_act_lo2;
+    m.xn_hi = e->ringb_xn_hi; m.xn_lo = e->ringb_xn_lo; m.ss_acc = e->ringb_ss_acc;
+    E_TRY(cudaMemsetAsync(e->ringb_ss_acc, 0, 16 * sizeof(unsigned long long), s));
     m.barrier = e->mega_barrier;
     {
       const char* tpb = getenv("LLMC_MEGA_TILES_PER_BLOCK");

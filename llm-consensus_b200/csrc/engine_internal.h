@@ -85,7 +85,8 @@ struct llmc_engine {
   float* ringb_part_val = nullptr;  // [4][SMs] argmax candidates
   int* ringb_part_idx = nullptr;
   unsigned* ringb_counters = nullptr;   // [4][kv_heads], zero between launches
-  uint16_t *ringb_attn_hi = nullptr, *ringb_attn_lo = nullptr, *ringb_act_hi = nullptr, *ringb_act_lo = nullptr, *ringb_attn_lo2 = nullptr, *ringb_act_lo2 = nullptr;   // [4][QD], [4][I] bf16 planes
+  uint16_t *ringb_attn_hi = nullptr, *ringb_attn_lo = nullptr, *ringb_act_hi = nullptr, *ringb_act_lo = nullptr, *ringb_attn_lo2 = nullptr, *ringb_act_lo2 = nullptr, *ringb_xn_hi = nullptr, *ringb_xn_lo = nullptr;
+  unsigned long long* ringb_ss_acc = nullptr;   // [4 slots][4 sequences]   // [4][QD], [4][I] bf16 planes
   bool use_flow = false;  // ... with tagged-word hand-overs instead of grid barriers (decode_flow.cu)
   unsigned long long* flow_words = nullptr;   // the tagged-word buffers of decode_flow.cu
   size_t flow_nwords = 0;

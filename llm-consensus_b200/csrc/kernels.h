@@ -137,7 +137,11 @@ struct MegaArgs {
   // attention output and SwiGLU activation of the B sequences as bf16 hi / mid planes ([B][QD], [B][I]): written once by
   // the producing phase, read by every block of the next one without any conversion
   uint16_t *attn_hi, *attn_lo, *act_hi, *act_lo;
-  uint16_t *attn_lo2, *act_lo2;   // third plane (hi + mid + lo = 24 mantissa bits): the single-sequence variant
+  uint16_t *attn_lo2, *act_lo2;   // third plane (hi + mid + lo = 24 mantissa bits): the single-sequence variant  // the residual stream after each projection, already multiplied by the NEXT RMSNorm's gain, as bf16 hi / mid planes
+  // [B][H], and its sum of squares per sequence: 64-bit fixed-point accumulators (2^-24), 4 slots x 4 sequences used in
+  // turn, zero at launch
+  uint16_t *xn_hi, *xn_lo;
+  unsigned long long* ss_acc;
 };
 cudaError_t launch_decode_mega(const MegaArgs& a, int sm_count, cudaStream_t s);
 // ------------------------------------------------------------------ decode_ring.cu
