@@ -605,6 +605,28 @@ def test_ring_batch_decode(gpu, name, B, flags):
     e.close()
 
 
+def test_ring_batch_decode_long_and_uneven_contexts(gpu):
+    """Three sequences through the batched ring kernel with very different contexts -- 2 250, 33 and 1 100 positions:
+    the attention splits per (sequence, kv head) differ per sequence (6 blocks each are available at batch 3), the
+    short one runs unsplit -- over a chunk of 7 steps, each against its own oracle run."""
+    name = "wide-1b"
+    V = DIMS[name]["vocab"]
+    e = gpu.Engine(dims=DIMS[name], seed=23, max_ctx=2304, max_slots=3, prefill_impl=DEFAULT_IMPL)
+    o = ref.Oracle(name, seed=23, max_ctx=2304)
+    rng = np.random.default_rng(31)
+    lens = [2250, 33, 1100]
+    prompts = [rng.integers(0, V, n) for n in lens]
+    slots, firsts = [], []
+    for p in prompts:
+        s = e.seq_alloc()
+        slots.append(s)
+        firsts.append(e.prefill(s, p))
+    out, lg = e.decode(slots, 7, want_logits=True)
+    worst, ties = check_batched(o, prompts, firsts, out, lg, 7)
+    print("uneven contexts %s: worst last-step logit err %.3e (%d on their own path after a tie)" % (lens, worst, ties))
+    e.close()
+
+
 def test_ring_batch_decode_full_size_1b(gpu):
     """The batched ring kernel at the full Llama-3.2-1B shape: 4 sequences, a long and three short contexts, against the
     oracle; then the same slots continue as two pairs (batch 2) and must produce the tokens the oracle continues with."""
