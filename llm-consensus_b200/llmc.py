@@ -10,7 +10,7 @@ import os
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "lib", "libllmc.so")
+LIB_PATH = os.environ.get("LLMC_LIB_PATH") or os.path.join(_HERE, "lib", "libllmc.so")   # (override: A/B timing of two builds)
 
 SHAPE_CUSTOM, SHAPE_LLAMA_1B, SHAPE_LLAMA_8B = 0, 1, 2
 FLAG_NO_GRAPH, FLAG_NO_PDL, FLAG_KV_BF16, FLAG_PREFILL_BF16 = 1, 2, 4, 8
