@@ -180,7 +180,12 @@ __global__ void __launch_bounds__(RTHREADS, 1) decode_ring_batch_kernel(const Me
   const int nspb = max(1, min(RING_MAX_SPLIT, grid / (B * a.kv_heads)));
 
   int tix = 0;
-  const bool stats = a.trace && blockIdx.x == 0 && warp == 0;   // LLMC_MEGA_TRACE: cycle counters of block 0 / warp 0
+#ifdef LLMC_RINGB_STATS   // cycle counters of block 0 / warp 0 under LLMC_MEGA_TRACE: compiled out by default -- ten more live
+                          // registers through the whole kernel are not free here (build with -DLLMC_RINGB_STATS to get them)
+  const bool stats = a.trace && blockIdx.x == 0 && warp == 0;
+#else
+  constexpr bool stats = false;
+#endif
   long long t_full = 0, t_x = 0, t_bar = 0, t_slots = 0, t_flush = 0;
   const long long t_begin = clock64();
   auto grid_barrier = [&]() {
