@@ -19,6 +19,9 @@ NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 ARCH = ["-gencode", "arch=compute_100a,code=sm_100a"]
 FLAGS = ["-O3", "-std=c++17", "-lineinfo", "-Xcompiler", "-fPIC", "-Xcompiler", "-Wall",
          "-ccbin", "/usr/bin/g++", "--expt-relaxed-constexpr"]
+# e.g. LLMC_NVCC_EXTRA="-DLLMC_RINGB_STATS" python llm-consensus_b200/build.py --force : the batched ring kernel with its
+# cycle counters (profiles/ring_batch_trace.py prints them; they cost 4-5 % and are off in the normal build)
+FLAGS += os.environ.get("LLMC_NVCC_EXTRA", "").split()
 
 
 def sources():

@@ -1,4 +1,6 @@
-"""Per-phase trace (block 0) of the batched ring kernel at the 1B shape, context 512: python profiles/ring_batch_trace.py B"""
+"""Per-phase trace (block 0) of the batched ring kernel at the 1B shape, context 512: python profiles/ring_batch_trace.py B
+(the cycle counters of the "[ring batch stats]" line are zero unless the library was built with
+LLMC_NVCC_EXTRA="-DLLMC_RINGB_STATS" python llm-consensus_b200/build.py --force)"""
 import os, sys
 import numpy as np
 os.environ["LLMC_MEGA_TRACE"] = "1"
