@@ -1,5 +1,6 @@
-// decode_ring_batch.cu -- the shared-memory-ring decode kernel for 2..4 sequences at once (one persistent cooperative
-// launch for all steps of a llmc_decode call, every weight byte streamed ONCE per step for the whole batch).
+// decode_ring_batch.cu -- the shared-memory-ring decode kernel for 1..4 sequences at once (one persistent cooperative
+// launch for all steps of a llmc_decode call, every weight byte streamed ONCE per step for the whole batch).  Also the
+// default batch-1 kernel for 2 048-wide models (second sequence absent): faster than decode_ring.cu.
 //
 // Same skeleton as decode_ring_mma.cu: a producer thread fills a 6-slot ring (slot = 8 weight rows x 2048 k, 8 bulk
 // copies), the 8 consumer warps all work on the same slot (warp w: k range [256 w, +256)), the slot arithmetic is
@@ -9,9 +10,13 @@
 // the same precision as the hi + lo operand pairs of the GEMM decode path) -- columns 0..3 = {seq0 hi, seq0 mid,
 // seq1 hi, seq1 mid} of the first four k, columns 4..7 the same of the last four.  Four sequences = two MMAs per 32 k
 // against the same weight registers.
-//   * activation fragments come straight from L2 into registers: lane (column fg, k slot ft) loads the 16 bytes of its
-//     sequence / half per 32-k block, keeps its own part (hi or mid) -- no staging in shared memory, no block barrier;
-//     the RMSNorm sum of squares is reduced on the side and applied in the epilogue (1/rms is a scalar factor);
+//   * whoever PRODUCES an activation leaves it as finished bf16 hi / mid planes, so the 148 consumers of the next
+//     phase load fragments (8 bytes per 32 k and lane) instead of converting fp32 each: the attention output, the
+//     SwiGLU activation, and the residual stream -- the O and down projections update it by load-add-store (one
+//     owner per element) and publish it pre-multiplied by the next RMSNorm's gain; its sum of squares is collected in
+//     64-bit fixed-point accumulators (integer addition: deterministic whatever the arrival order), 1/rms is applied
+//     in the epilogue (it is a scalar factor).  Only layer 0 converts: its input is the embedding row;
+//   * activation fragments go from L2 straight to registers -- no staging in shared memory, no block barrier;
 //   * K > 2048 (down projection): segment-major as in decode_ring_mma.cu, the next segment's activation loads are in
 //     flight while the current segment's slots run;
 //   * partial sums (4 lanes x 8 warps per row and sequence) meet through shuffles and a batched shared-memory exchange;
